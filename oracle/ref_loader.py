@@ -1,0 +1,58 @@
+"""TEST INFRASTRUCTURE — imports the REAL reference (``/root/reference``) behind the shims in
+``oracle/shims`` so that golden vectors can be generated from the reference's own code.
+
+Only usable in the build container (``/root/reference`` does not exist on the GPU box); nothing in
+``tests -m gpu``, ``smoke()`` or ``bench.py`` may import this module.  Recipe: SURVEY.md App. C.
+"""
+import importlib
+import os
+import sys
+import types
+
+REF_ROOT = os.environ.get("MDV2_REFERENCE_ROOT", "/root/reference")
+_SHIMS = os.path.join(os.path.dirname(os.path.abspath(__file__)), "shims")
+
+
+def available() -> bool:
+    return os.path.isdir(os.path.join(REF_ROOT, "magicdrivedit"))
+
+
+def _ns(name, path):
+    m = types.ModuleType(name)
+    m.__path__ = [path]
+    sys.modules[name] = m
+    return m
+
+
+def load_reference():
+    """Returns the reference module ``magicdrivedit.models.magicdrive.magicdrive_stdit3``."""
+    if not available():
+        raise RuntimeError(f"reference tree not found at {REF_ROOT}")
+    name = "magicdrivedit.models.magicdrive.magicdrive_stdit3"
+    if name in sys.modules:
+        return sys.modules[name]
+    os.environ["USE_XFORMERS"] = "False"
+    if _SHIMS not in sys.path:
+        sys.path.insert(0, _SHIMS)
+    pkg = os.path.join(REF_ROOT, "magicdrivedit")
+    # namespace stubs: skip the package __init__s that pull diffusers / ftfy / datasets
+    _ns("magicdrivedit", pkg)
+    _ns("magicdrivedit.models", os.path.join(pkg, "models"))
+    _ns("magicdrivedit.models.vae", os.path.join(pkg, "models", "vae"))
+    _ns("magicdrivedit.utils", os.path.join(pkg, "utils"))
+    ck = types.ModuleType("magicdrivedit.utils.ckpt_utils")
+
+    def load_checkpoint(*a, **k):
+        raise NotImplementedError("oracle stub")
+
+    ck.load_checkpoint = load_checkpoint
+    sys.modules["magicdrivedit.utils.ckpt_utils"] = ck
+    return importlib.import_module(name)
+
+
+def build_reference_model(kwargs: dict, brushnet: bool = False):
+    """Builds the reference nn.Module from constructor kwargs (see synth.model_kwargs)."""
+    ref = load_reference()
+    cfg = ref.MagicDriveSTDiT3Config(**kwargs)
+    cls = ref.MagicDriveSTDiT3BrushNet if brushnet else ref.MagicDriveSTDiT3
+    return cls(cfg)
