@@ -162,3 +162,33 @@ def randomize_zero_params(model: torch.nn.Module, seed: int = 1, std: float = 0.
             p.copy_(torch.randn(p.shape, generator=g) * std)
             n += 1
     return n
+
+
+_SMALL_INIT = ("mva_proj.", "after_proj.", "before_proj.", "final_proj.")
+
+
+@torch.no_grad()
+def fill_params(model: torch.nn.Module, seed: int = 0):
+    """Deterministic, construction-order-independent weights: every state-dict entry is filled from
+    a generator seeded by (seed, crc32(name)), so the reference module, the oracle and the native
+    drop-in get bit-identical parameters without shipping a checkpoint.  Scales follow the
+    reference init (xavier for matrices) with N(0, 0.02) on biases and on the branches the
+    reference zero-initialises (magicdrive_stdit3.py:788-825), so that no branch is silently 0."""
+    import zlib
+    for name, t in sorted(model.state_dict().items()):
+        if not t.is_floating_point() or name.endswith("rope.freqs") or name.endswith("inv_freq"):
+            continue
+        g = torch.Generator().manual_seed((seed * 1000003 + zlib.crc32(name.encode())) % (2 ** 63))
+        r = torch.randn(t.shape, generator=g)
+        small = any(k in name for k in _SMALL_INIT) or (
+            "blocks_t." in name and (".attn.proj." in name or ".cross_attn.proj." in name))
+        if t.dim() >= 2:
+            fan_out, fan_in = t.shape[0], t[0].numel()
+            std = 0.02 if small else (2.0 / (fan_in + fan_out)) ** 0.5
+            val = r * std
+        elif "norm.weight" in name:
+            val = 1.0 + 0.1 * r
+        else:
+            val = r * 0.02
+        t.copy_(val.to(t.dtype))
+    return model
