@@ -1,0 +1,88 @@
+/* mdv2.h — C ABI of libmdv2.so, the sm_100a kernels behind the MagicDriveSTDiT3 drop-in.
+ *
+ * The reference (HerrWangkv/MagicDrive-V2) is pure PyTorch and has no FFI of its own; each entry
+ * point below replaces the library call(s) the reference makes at the cited lines (paths relative
+ * to the reference root; "stdit3.py" = magicdrivedit/models/magicdrive/magicdrive_stdit3.py,
+ * "blocks.py" = magicdrivedit/models/layers/blocks.py).
+ *
+ * Conventions: plain pointers and sizes only; every pointer is a DEVICE pointer unless noted;
+ * `dtype`: 0 = fp32, 1 = bf16 (activations, weights and outputs share it; modulation tables and
+ * RoPE tables are always fp32).  `stream` is a cudaStream_t passed as void*.  Functions launch
+ * asynchronously on `stream`, never synchronise, never allocate persistent device memory, and
+ * return 0 on success or a negative MDV2_E* code (message via mdv2_last_error()).
+ *
+ * Token geometry ("geo"): rows of an activation matrix are ordered (β, t, s) with β = bi·NC + v;
+ * row r -> modulation row (r / S / T / NC)·T + (r / S) % T of a table [b·T, K, C] (fp32).
+ */
+#ifndef MDV2_H
+#define MDV2_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MDV2_OK 0
+#define MDV2_EINVAL (-1)   /* unsupported shape / argument */
+#define MDV2_ECUDA (-2)    /* CUDA runtime / driver error at launch */
+#define MDV2_EARCH (-3)    /* device is not sm_100 */
+
+#define MDV2_BACKEND_AUTO 0
+#define MDV2_BACKEND_SIMT 1     /* CUDA-core kernels (fp32 validation mode, odd shapes) */
+#define MDV2_BACKEND_TCGEN05 2  /* tcgen05 / TMEM / TMA kernels (bf16) */
+
+int mdv2_version(void);
+const char* mdv2_last_error(void);   /* host pointer, thread-local */
+
+/* LayerNorm(eps, no affine) -> x·(1+scale)+shift with per-(bi,t) rows of `mod`.
+ * Replaces nn.LayerNorm/apex FusedLayerNorm + t2i_modulate + t_mask_select:
+ * blocks.py:71-80,92-93; stdit3.py:148-156,213-226,288-301,337-340; blocks.py:893-903. */
+int mdv2_ln_modulate(const void* x, void* out, const float* mod, int64_t n_rows, int C, int K,
+                     int k_shift, int k_scale, int T, int S, int NC, float eps, int dtype,
+                     void* stream);
+
+/* out[M,N] = epilogue(a[M,K] · w[N,K]^T):  v = acc + bias_scale·bias ; optional per-head RMSNorm
+ * (columns [0,n_q) with rms_q, [n_q,n_q+n_k) with rms_k, head_dim wide) ; optional tanh-GELU ;
+ * optional gate (fp32 table row, index k_gate) ; optional residual (row r, or mapped row
+ * (r / (res_mod·res_div))·res_mod + r % res_mod, or r % res_mod when res_div == 0).
+ * out may alias res.  Replaces every nn.Linear / F.linear / timm Mlp / LlamaRMSNorm / gate+residual
+ * on the path: blocks.py:54-68,183,188,410-456,658-661; stdit3.py:256-262,280,325-356,1145-1157. */
+int mdv2_gemm(const void* a, int64_t lda, const void* w, int64_t ldw, const void* bias, void* out,
+              int64_t ldo, int64_t M, int N, int K, int act, float bias_scale,
+              const float* gate_mod, int mod_K, int k_gate, const void* res, int64_t ldr,
+              int64_t res_mod, int64_t res_div, int T, int S, int NC, const void* rms_q,
+              const void* rms_k, int head_dim, int n_q, int n_k, float eps, int dtype, int backend,
+              void* stream);
+
+/* Softmax attention over n_seq sequences: query rows [i·Lq,(i+1)·Lq) of q, key/value rows
+ * [j·Lk,(j+1)·Lk) with j = i (kv_map == NULL) or j = kv_map[i·n_sets + set]; the outputs of the
+ * n_sets K/V sets are summed (cross-view attention).  Heads are D-wide column groups.
+ * Replaces flash_attn_func / xformers / the eager softmax path and the cross-view gather+sum:
+ * blocks.py:456-504,607-613,710-742; stdit3.py:158-190,303-322. */
+int mdv2_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                   int64_t ldv, void* out, int64_t ldo, int n_seq, int Lq, int Lk, int H, int D,
+                   float scale, const int32_t* kv_map, int n_sets, int dtype, int backend,
+                   void* stream);
+
+/* Temporal self-attention of every (β, s) column over its T frames, with interleaved-pair RoPE on
+ * q and k (cos/sin: fp32 [T, D]); qkv rows are (β,t,s) with q|k|v column blocks of width H·D.
+ * Replaces the two transposes + Attention.forward + RotaryEmbedding: stdit3.py:232-234,
+ * blocks.py:198-278. */
+int mdv2_temporal_attention(const void* qkv, int64_t ld, const float* cos_t, const float* sin_t,
+                            void* out, int64_t ldo, int B, int T, int S, int H, int D, float scale,
+                            int dtype, void* stream);
+
+/* Patch gather for PatchEmbed3D with patch (1,2,2): x[Bx, Cin·NCi, T, Hx, Wx] (channel = c·NCi+v)
+ * -> out rows (β = bx·NCi+v, t, s in [s0, s0+Sl)) of Cin·4 values ordered (c, dh, dw); zero beyond
+ * Hx/Wx (the H/W padding of blocks.py:132-147 and stdit3.py:1101-1104; view split stdit3.py:1041). */
+int mdv2_patchify(const void* x, void* out, int Bx, int Cin, int NCi, int T, int Hx, int Wx, int Hp,
+                  int Wp, int s0, int Sl, int dtype, void* stream);
+
+/* unpatchify + crop + fp32 cast + view re-interleave: y[(b·NC+v), t, Hp·Wp, (dh, dw, c)] ->
+ * out fp32 [b, c·NC+v, Tx, Hx, Wx].  stdit3.py:1212-1244. */
+int mdv2_unpatchify(const void* y, float* out, int b, int NC, int Cout, int T, int Hp, int Wp, int Tx,
+                    int Hx, int Wx, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

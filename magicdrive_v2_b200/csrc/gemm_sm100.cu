@@ -1,0 +1,348 @@
+// gemm_sm100.cu — bf16 GEMM  out = epilogue(A[M,K] · W[N,K]^T)  on the 5th-gen tensor cores.
+//
+// Persistent, warp-specialised: warp 0 = TMA producer (A and W tiles, 128-byte swizzle), warp 1 =
+// tcgen05.mma issuer (one elected lane) + TMEM owner, warps 2-5 = epilogue (TMEM -> registers ->
+// fused bias / per-head RMSNorm / GELU -> shared staging -> gate / residual -> coalesced stores).
+// Two TMEM accumulator stages let the epilogue of tile i overlap the main loop of tile i+1.
+// Tile: 128 x BN x 64, UMMA 128 x BN x 16, fp32 accumulate in TMEM.
+#include <mutex>
+#include <unordered_map>
+
+#include "gemm_epilogue.cuh"
+#include "sm100_ptx.cuh"
+
+using namespace sm100;
+
+namespace {
+constexpr int BM = 128, BK = 64;
+constexpr int A_BYTES = BM * BK * 2;
+constexpr int NUM_THREADS = 192;
+constexpr int TMEM_COLS = 512, ACC_STRIDE = 256;
+
+template <int BN, int HD>
+struct Cfg {
+  static constexpr int CW = HD ? HD : 64;                // epilogue chunk width (columns)
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int PITCH = CW * 2 + 32 - ((CW * 2) % 32) + 16;   // odd multiple of 16 B
+  static constexpr int ROWINFO = 4 * 32 * 16;                          // per-row gate / residual row cache
+  static constexpr int STAGING = 4 * 32 * PITCH + ROWINFO;
+  static constexpr int STAGES_RAW = (232448 - 1024 - 256 - STAGING) / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+  static constexpr int SMEM = STAGES * STAGE_BYTES + STAGING + 256 + 1024;  // + barriers + align slack
+  static_assert(BN % CW == 0, "tile must hold whole epilogue chunks");
+  static_assert((PITCH / 16) % 2 == 1, "staging pitch must be an odd multiple of 16 B");
+  static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-B alignment");
+};
+
+struct Params {
+  int64_t M;
+  int N, K;
+  int64_t ldo;
+  bf16* out;
+  Epilogue<bf16> ep;
+  const bf16* rms_q;
+  const bf16* rms_k;
+  int n_q, n_k;
+  float eps;
+};
+
+template <int BN, int HD>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
+                  const Params p) {
+  using C = Cfg<BN, HD>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* staging = smem + C::STAGES * C::STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::STAGING);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + C::STAGES;
+  uint64_t* tfull = bars + 2 * C::STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles_n = p.N / BN;
+  const int64_t n_tiles_m = (p.M + BM - 1) / BM;
+  const int64_t n_tiles = n_tiles_m * n_tiles_n;
+  const int n_kb = p.K / BK;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_a);
+    prefetch_tmap(&tmap_w);
+    for (int i = 0; i < C::STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int m0 = (int)(tile / n_tiles_n) * BM, n0 = (int)(tile % n_tiles_n) * BN;
+        for (int kb = 0; kb < n_kb; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * C::STAGE_BYTES;
+          mbar_expect_tx(&full[stage], C::STAGE_BYTES);
+          tma_load_2d(sa, &tmap_a, &full[stage], kb * BK, m0);
+          tma_load_2d(sa + A_BYTES, &tmap_w, &full[stage], kb * BK, n0);
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
+        for (int kb = 0; kb < n_kb; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * C::STAGE_BYTES);
+          const uint64_t da = make_desc_k_sw128(sa), db = make_desc_k_sw128(sa + A_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            umma_bf16_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+          umma_commit(&empty[stage]);
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ===== epilogue warps (TMEM lane quarter = warp % 4) =====
+    constexpr int CW = C::CW;
+    const int quarter = warp & 3;
+    uint8_t* stg = staging + quarter * 32 * C::PITCH;
+    int64_t* row_res = reinterpret_cast<int64_t*>(staging + 4 * 32 * C::PITCH) + quarter * 64;
+    int64_t* row_gate = row_res + 32;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const Epilogue<bf16>& ep = p.ep;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      const int64_t m0 = (tile / n_tiles_n) * BM;
+      const int n0 = (int)(tile % n_tiles_n) * BN;
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + acc * ACC_STRIDE + ((uint32_t)(quarter * 32) << 16);
+      {  // per-row epilogue context, once per tile (64-bit divisions stay out of the inner loops)
+        const int64_t gr = m0 + quarter * 32 + lane;
+        const RowCtx rc = ep.row_ctx(gr < p.M ? gr : 0);
+        row_res[lane] = rc.res_row * ep.ldr;
+        row_gate[lane] = rc.gate ? (int64_t)(rc.gate - ep.gate_mod) : -1;
+        __syncwarp();
+      }
+#pragma unroll 1
+      for (int ch = 0; ch < BN / CW; ++ch) {
+        const int c0 = n0 + ch * CW;
+        uint32_t raw[CW];
+        tmem_ld_x32(t_row + ch * CW, raw);
+        tmem_ld_x32(t_row + ch * CW + 32, raw + 32);
+        if constexpr (CW == 72) tmem_ld_x8(t_row + ch * CW + 64, raw + 64);
+        tmem_ld_wait();
+        float v[CW];
+#pragma unroll
+        for (int j = 0; j < CW; ++j) v[j] = __uint_as_float(raw[j]);
+        if (ep.bias) {
+#pragma unroll
+          for (int j = 0; j < CW; ++j) v[j] += ep.bias_scale * __bfloat162float(__ldg(ep.bias + c0 + j));
+        }
+        if constexpr (HD != 0) {
+          const bf16* w = c0 < p.n_q ? p.rms_q : (c0 < p.n_q + p.n_k ? p.rms_k : nullptr);
+          if (w != nullptr) {
+            float ss = 0.f;
+#pragma unroll
+            for (int j = 0; j < CW; ++j) ss += v[j] * v[j];
+            const float r = rsqrtf(ss / CW + p.eps);
+#pragma unroll
+            for (int j = 0; j < CW; ++j)
+              v[j] = __bfloat162float(__ldg(w + j)) * __bfloat162float(__float2bfloat16_rn(v[j] * r));
+          }
+        }
+        if (ep.act == 1) {
+#pragma unroll
+          for (int j = 0; j < CW; ++j) v[j] = gelu_tanh(v[j]);
+        }
+        // row phase -> staging (bf16 when no gate/residual follows, else keep bf16 too: the
+        // reference rounds the projection output to bf16 before gate/residual as well)
+        uint8_t* srow = stg + lane * C::PITCH;
+#pragma unroll
+        for (int j = 0; j < CW; j += 8) {
+          Vec16<bf16> pk;
+          pk.pack(v + j);
+          *reinterpret_cast<uint4*>(srow + j * 2) = pk.raw;
+        }
+        __syncwarp();
+        // column phase: coalesced 4-byte accesses, gate / residual / store
+        constexpr int WPR = CW / 2;  // 32-bit words per row
+#pragma unroll 4
+        for (int idx = lane; idx < 32 * WPR; idx += 32) {
+          const int rl = idx / WPR, wd = idx % WPR;
+          const int64_t gr = m0 + quarter * 32 + rl;
+          if (gr < p.M) {
+            float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(stg + rl * C::PITCH + wd * 4));
+            const int col = c0 + wd * 2;
+            const int64_t goff = row_gate[rl];
+            if (goff >= 0) {
+              const float2 g = *reinterpret_cast<const float2*>(ep.gate_mod + goff + col);
+              f.x *= g.x;
+              f.y *= g.y;
+            }
+            if (ep.res) {
+              const float2 rr = __bfloat1622float2(
+                  *reinterpret_cast<const __nv_bfloat162*>(ep.res + row_res[rl] + col));
+              f.x += rr.x;
+              f.y += rr.y;
+            }
+            *reinterpret_cast<__nv_bfloat162*>(p.out + gr * p.ldo + col) = __floats2bfloat162_rn(f.x, f.y);
+          }
+        }
+        __syncwarp();
+      }
+      tc_fence_before();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ---- host side: tensor maps ---------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)sym;
+  });
+  return fn;
+}
+}  // namespace
+
+// 2-D bf16 row-major [rows, cols] with leading dimension ld (elements); box = box_rows x 64 cols, SW128
+int mdv2_make_tmap_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                      uint32_t box_cols) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    mdv2_set_error("cuTensorMapEncodeTiled unavailable");
+    return MDV2_ECUDA;
+  }
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    mdv2_set_error("cuTensorMapEncodeTiled failed (%d) ptr=%p rows=%llu cols=%llu ld=%llu box=%ux%u", (int)r, ptr,
+                   (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows, box_cols);
+    return MDV2_ECUDA;
+  }
+  return MDV2_OK;
+}
+
+namespace {
+template <int BN, int HD>
+int launch(const CUtensorMap& ta, const CUtensorMap& tw, const Params& p, cudaStream_t st) {
+  using C = Cfg<BN, HD>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_sm100_kernel<BN, HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    if (e != cudaSuccess) {
+      mdv2_set_error("gemm_sm100: cannot set %d B dynamic smem: %s", C::SMEM, cudaGetErrorString(e));
+      return MDV2_ECUDA;
+    }
+    configured = true;
+  }
+  const int64_t tiles = ((p.M + BM - 1) / BM) * (p.N / BN);
+  const int grid = (int)(tiles < mdv2_num_sms() ? tiles : mdv2_num_sms());
+  gemm_sm100_kernel<BN, HD><<<grid, NUM_THREADS, C::SMEM, st>>>(ta, tw, p);
+  MDV2_CHECK_LAUNCH("gemm_sm100");
+  return MDV2_OK;
+}
+
+int pick_bn(int N, const RmsArgs* rms) {
+  if (rms && rms->wq) {
+    if (rms->head_dim == 72 && N % 144 == 0) return 144;
+    if (rms->head_dim == 64 && N % 128 == 0) return 128;
+    return 0;
+  }
+  if (N % 256 == 0) return 256;
+  if (N % 192 == 0) return 192;
+  if (N % 128 == 0) return 128;
+  if (N % 64 == 0) return 64;
+  return 0;
+}
+}  // namespace
+
+bool mdv2_gemm_sm100_supported(int64_t M, int N, int K, int64_t lda, int64_t ldw, int64_t ldo, const RmsArgs* rms) {
+  if (M <= 0 || K % BK != 0 || K <= 0) return false;
+  if (lda % 8 != 0 || ldw % 8 != 0 || ldo % 2 != 0) return false;
+  if (rms && rms->wq && (rms->n_q % rms->head_dim != 0 || rms->n_k % rms->head_dim != 0)) return false;
+  return pick_bn(N, rms) != 0;
+}
+
+int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void* out, int64_t ldo, int64_t M, int N,
+                    int K, const Epilogue<bf16>& ep, const RmsArgs* rms, cudaStream_t st) {
+  MDV2_REQUIRE(mdv2_gemm_sm100_supported(M, N, K, lda, ldw, ldo, rms), "gemm_sm100: unsupported shape M=%lld N=%d K=%d",
+               (long long)M, N, K);
+  MDV2_REQUIRE(((uintptr_t)a % 16 == 0) && ((uintptr_t)w % 16 == 0) && ((uintptr_t)out % 4 == 0),
+               "gemm_sm100: operands must be 16-byte aligned");
+  const int bn = pick_bn(N, rms);
+  CUtensorMap ta, tw;
+  int rc = mdv2_make_tmap_2d(&ta, a, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BM, BK);
+  if (rc) return rc;
+  rc = mdv2_make_tmap_2d(&tw, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)bn, BK);
+  if (rc) return rc;
+  Params p;
+  p.M = M; p.N = N; p.K = K; p.ldo = ldo; p.out = (bf16*)out; p.ep = ep;
+  p.rms_q = rms ? (const bf16*)rms->wq : nullptr;
+  p.rms_k = rms ? (const bf16*)rms->wk : nullptr;
+  p.n_q = rms ? rms->n_q : 0;
+  p.n_k = rms ? rms->n_k : 0;
+  p.eps = rms ? rms->eps : 0.f;
+  switch (bn) {
+    case 256: return launch<256, 0>(ta, tw, p, st);
+    case 192: return launch<192, 0>(ta, tw, p, st);
+    case 64: return launch<64, 0>(ta, tw, p, st);
+    case 144: return launch<144, 72>(ta, tw, p, st);
+    case 128:
+      if (rms && rms->wq) return launch<128, 64>(ta, tw, p, st);
+      return launch<128, 0>(ta, tw, p, st);
+  }
+  MDV2_REQUIRE(false, "gemm_sm100: no tile for N=%d", N);
+}

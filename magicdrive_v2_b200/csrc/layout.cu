@@ -1,0 +1,233 @@
+// layout.cu — patch gather / scatter and the temporal-attention micro-kernel.
+#include "common.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// patchify: one thread per output element (coalesced stores)
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void patchify_kernel(const T* __restrict__ x, T* __restrict__ out, int64_t total, int Cin,
+                                int NCi, int Tn, int Hx, int Wx, int Wp, int s0, int Sl) {
+  const int K4 = Cin * 4;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int e = (int)(idx % K4);
+    int64_t row = idx / K4;
+    const int sl = (int)(row % Sl);
+    row /= Sl;
+    const int t = (int)(row % Tn);
+    const int beta = (int)(row / Tn);
+    const int bx = beta / NCi, v = beta % NCi;
+    const int c = e >> 2, dh = (e >> 1) & 1, dw = e & 1;
+    const int s = s0 + sl;
+    const int h = 2 * (s / Wp) + dh, w = 2 * (s % Wp) + dw;
+    T val = from_f<T>(0.f);
+    if (h < Hx && w < Wx) {
+      int64_t ch = (int64_t)bx * Cin * NCi + (int64_t)c * NCi + v;
+      val = x[((ch * Tn + t) * Hx + h) * (int64_t)Wx + w];
+    }
+    out[idx] = val;
+  }
+}
+
+extern "C" int mdv2_patchify(const void* x, void* out, int Bx, int Cin, int NCi, int T, int Hx, int Wx,
+                             int Hp, int Wp, int s0, int Sl, int dtype, void* stream) {
+  MDV2_REQUIRE(s0 >= 0 && Sl >= 0 && s0 + Sl <= Hp * Wp, "patchify: token slice out of range");
+  MDV2_REQUIRE(2 * Hp >= Hx && 2 * Wp >= Wx, "patchify: patch grid smaller than the input");
+  const int64_t total = (int64_t)Bx * NCi * T * Sl * Cin * 4;
+  if (total == 0) return MDV2_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int threads = 256;
+  int64_t blocks = (total + threads - 1) / threads;
+  const int64_t cap = (int64_t)mdv2_num_sms() * 32;
+  if (blocks > cap) blocks = cap;
+  if (dtype == 0)
+    patchify_kernel<float><<<(unsigned)blocks, threads, 0, st>>>((const float*)x, (float*)out, total, Cin, NCi, T, Hx, Wx, Wp, s0, Sl);
+  else if (dtype == 1)
+    patchify_kernel<bf16><<<(unsigned)blocks, threads, 0, st>>>((const bf16*)x, (bf16*)out, total, Cin, NCi, T, Hx, Wx, Wp, s0, Sl);
+  else
+    MDV2_REQUIRE(false, "patchify: bad dtype");
+  MDV2_CHECK_LAUNCH("patchify");
+  return MDV2_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// unpatchify + crop + fp32 + view interleave: one thread per output element
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void unpatchify_kernel(const T* __restrict__ y, float* __restrict__ out, int64_t total, int NC,
+                                  int Cout, int Tn, int Hp, int Wp, int Tx, int Hx, int Wx) {
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = idx;
+    const int w = (int)(r % Wx); r /= Wx;
+    const int h = (int)(r % Hx); r /= Hx;
+    const int t = (int)(r % Tx); r /= Tx;
+    const int ch = (int)(r % (Cout * NC));
+    const int b = (int)(r / (Cout * NC));
+    const int c = ch / NC, v = ch % NC;
+    const int64_t row = (((int64_t)(b * NC + v) * Tn + t) * Hp + (h >> 1)) * Wp + (w >> 1);
+    const int feat = (((h & 1) << 1) | (w & 1)) * Cout + c;
+    out[idx] = to_f(y[row * (4 * Cout) + feat]);
+  }
+}
+
+extern "C" int mdv2_unpatchify(const void* y, float* out, int b, int NC, int Cout, int T, int Hp, int Wp,
+                               int Tx, int Hx, int Wx, int dtype, void* stream) {
+  MDV2_REQUIRE(Tx <= T && Hx <= 2 * Hp && Wx <= 2 * Wp, "unpatchify: crop larger than the token grid");
+  const int64_t total = (int64_t)b * NC * Cout * Tx * Hx * Wx;
+  if (total == 0) return MDV2_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int threads = 256;
+  int64_t blocks = (total + threads - 1) / threads;
+  const int64_t cap = (int64_t)mdv2_num_sms() * 32;
+  if (blocks > cap) blocks = cap;
+  if (dtype == 0)
+    unpatchify_kernel<float><<<(unsigned)blocks, threads, 0, st>>>((const float*)y, out, total, NC, Cout, T, Hp, Wp, Tx, Hx, Wx);
+  else if (dtype == 1)
+    unpatchify_kernel<bf16><<<(unsigned)blocks, threads, 0, st>>>((const bf16*)y, out, total, NC, Cout, T, Hp, Wp, Tx, Hx, Wx);
+  else
+    MDV2_REQUIRE(false, "unpatchify: bad dtype");
+  MDV2_CHECK_LAUNCH("unpatchify");
+  return MDV2_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// temporal attention: one warp per (β, s, head); lane owns the RoPE pairs p = lane + 32·j.
+// K/V of the T frames stay in registers; strided (β,:,s) access, no transposes materialised.
+// ------------------------------------------------------------------------------------------------
+template <typename T> struct Pair;
+template <> struct Pair<float> {
+  static __device__ __forceinline__ float2 ld(const float* p) { return *reinterpret_cast<const float2*>(p); }
+  static __device__ __forceinline__ void st(float* p, float2 v) { *reinterpret_cast<float2*>(p) = v; }
+};
+template <> struct Pair<bf16> {
+  static __device__ __forceinline__ float2 ld(const bf16* p) {
+    return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+  }
+  static __device__ __forceinline__ void st(bf16* p, float2 v) {
+    *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(v.x, v.y);
+  }
+};
+
+template <typename T, int TMAX, int PPL>
+__global__ void __launch_bounds__(128) temporal_attn_kernel(const T* __restrict__ qkv, int64_t ld,
+                                                            const float* __restrict__ cos_t,
+                                                            const float* __restrict__ sin_t,
+                                                            T* __restrict__ out, int64_t ldo, int64_t n_warps,
+                                                            int Tn, int S, int H, int D, float scale) {
+  const int lane = threadIdx.x & 31;
+  const int64_t wid = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (wid >= n_warps) return;
+  const int h = (int)(wid % H);
+  const int64_t bs = wid / H;
+  const int s = (int)(bs % S);
+  const int64_t beta = bs / S;
+  const int C = H * D;
+  const int np = D / 2;
+  float2 kk[TMAX][PPL], vv[TMAX][PPL];
+#pragma unroll
+  for (int t = 0; t < TMAX; ++t) {
+    if (t < Tn) {
+      const T* rowp = qkv + ((beta * Tn + t) * S + s) * ld + (int64_t)h * D;
+#pragma unroll
+      for (int j = 0; j < PPL; ++j) {
+        const int p = lane + 32 * j;
+        if (p < np) {
+          float2 kv = Pair<T>::ld(rowp + C + 2 * p);
+          const float c0 = cos_t[t * D + 2 * p], c1 = cos_t[t * D + 2 * p + 1];
+          const float s0 = sin_t[t * D + 2 * p], s1 = sin_t[t * D + 2 * p + 1];
+          kk[t][j] = make_float2(kv.x * c0 - kv.y * s0, kv.y * c1 + kv.x * s1);
+          vv[t][j] = Pair<T>::ld(rowp + 2 * C + 2 * p);
+        } else {
+          kk[t][j] = make_float2(0.f, 0.f);
+          vv[t][j] = make_float2(0.f, 0.f);
+        }
+      }
+    }
+  }
+  for (int tq = 0; tq < Tn; ++tq) {
+    const T* rowp = qkv + ((beta * Tn + tq) * S + s) * ld + (int64_t)h * D;
+    float2 qq[PPL];
+#pragma unroll
+    for (int j = 0; j < PPL; ++j) {
+      const int p = lane + 32 * j;
+      if (p < np) {
+        float2 qv = Pair<T>::ld(rowp + 2 * p);
+        const float c0 = cos_t[tq * D + 2 * p], c1 = cos_t[tq * D + 2 * p + 1];
+        const float s0 = sin_t[tq * D + 2 * p], s1 = sin_t[tq * D + 2 * p + 1];
+        qq[j] = make_float2((qv.x * c0 - qv.y * s0) * scale, (qv.y * c1 + qv.x * s1) * scale);
+      } else {
+        qq[j] = make_float2(0.f, 0.f);
+      }
+    }
+    float sc[TMAX];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int t = 0; t < TMAX; ++t) {
+      if (t < Tn) {
+        float a = 0.f;
+#pragma unroll
+        for (int j = 0; j < PPL; ++j) a += qq[j].x * kk[t][j].x + qq[j].y * kk[t][j].y;
+        sc[t] = warp_sum(a);
+        mx = fmaxf(mx, sc[t]);
+      }
+    }
+    float den = 0.f;
+#pragma unroll
+    for (int t = 0; t < TMAX; ++t) {
+      if (t < Tn) {
+        sc[t] = __expf(sc[t] - mx);
+        den += sc[t];
+      }
+    }
+    const float inv = 1.f / den;
+    T* orow = out + ((beta * Tn + tq) * S + s) * ldo + (int64_t)h * D;
+#pragma unroll
+    for (int j = 0; j < PPL; ++j) {
+      const int p = lane + 32 * j;
+      if (p < np) {
+        float2 o = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int t = 0; t < TMAX; ++t) {
+          if (t < Tn) {
+            o.x += sc[t] * vv[t][j].x;
+            o.y += sc[t] * vv[t][j].y;
+          }
+        }
+        Pair<T>::st(orow + 2 * p, make_float2(o.x * inv, o.y * inv));
+      }
+    }
+  }
+}
+
+template <typename T>
+static int launch_temporal(const void* qkv, int64_t ld, const float* c, const float* s, void* out, int64_t ldo,
+                           int B, int Tn, int S, int H, int D, float scale, cudaStream_t st) {
+  const int64_t n_warps = (int64_t)B * S * H;
+  dim3 grid((unsigned)((n_warps + 3) / 4)), block(128);
+  const int ppl = (D / 2 + 31) / 32;
+#define TA_CASE(TM, PP)                                                                                \
+  temporal_attn_kernel<T, TM, PP><<<grid, block, 0, st>>>((const T*)qkv, ld, c, s, (T*)out, ldo, n_warps, \
+                                                          Tn, S, H, D, scale)
+  if (ppl == 1) {
+    if (Tn <= 8) TA_CASE(8, 1); else TA_CASE(32, 1);
+  } else {
+    if (Tn <= 8) TA_CASE(8, 2); else TA_CASE(32, 2);
+  }
+#undef TA_CASE
+  MDV2_CHECK_LAUNCH("temporal_attention");
+  return MDV2_OK;
+}
+
+extern "C" int mdv2_temporal_attention(const void* qkv, int64_t ld, const float* cos_t, const float* sin_t,
+                                       void* out, int64_t ldo, int B, int T, int S, int H, int D, float scale,
+                                       int dtype, void* stream) {
+  if ((int64_t)B * S * H == 0) return MDV2_OK;
+  MDV2_REQUIRE(T >= 1 && T <= 32, "temporal_attention: T=%d unsupported (1..32)", T);
+  MDV2_REQUIRE(D % 2 == 0 && D <= 128, "temporal_attention: head_dim=%d unsupported", D);
+  MDV2_REQUIRE(ld % 2 == 0 && ldo % 2 == 0, "temporal_attention: odd leading dimension");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == 0) return launch_temporal<float>(qkv, ld, cos_t, sin_t, out, ldo, B, T, S, H, D, scale, st);
+  if (dtype == 1) return launch_temporal<bf16>(qkv, ld, cos_t, sin_t, out, ldo, B, T, S, H, D, scale, st);
+  MDV2_REQUIRE(false, "temporal_attention: bad dtype");
+}

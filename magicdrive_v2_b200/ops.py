@@ -1,0 +1,179 @@
+"""ctypes binding of ``libmdv2.so`` — the only execution path of the STDiT3 hot loop.
+
+Every function takes torch CUDA tensors, passes raw ``data_ptr()``s plus sizes through the C ABI
+declared in ``include/mdv2.h`` and launches on torch's current stream.  There is deliberately no
+CPU or eager fallback: importing this module without the built library, or calling an op with a
+non-CUDA tensor, raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmdv2.so")
+
+BACKEND_AUTO, BACKEND_SIMT, BACKEND_TCGEN05 = 0, 1, 2
+_BACKENDS = {None: 0, "auto": 0, "simt": 1, "tcgen05": 2}
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `python -m magicdrive_v2_b200.build` "
+        "(or __graft_entry__.build()); the STDiT3 drop-in has no fallback path.")
+
+_lib = ctypes.CDLL(LIB_PATH)
+_vp, _i64, _i32, _f32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_float
+
+_lib.mdv2_version.restype = _i32
+_lib.mdv2_last_error.restype = ctypes.c_char_p
+_lib.mdv2_ln_modulate.argtypes = [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _i32, _vp]
+_lib.mdv2_gemm.argtypes = [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _f32, _vp, _i32, _i32,
+                           _vp, _i64, _i64, _i64, _i32, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _f32, _i32, _i32, _vp]
+_lib.mdv2_attention.argtypes = [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _f32,
+                                _vp, _i32, _i32, _i32, _vp]
+_lib.mdv2_temporal_attention.argtypes = [_vp, _i64, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _f32,
+                                         _i32, _vp]
+_lib.mdv2_patchify.argtypes = [_vp, _vp] + [_i32] * 11 + [_vp]
+_lib.mdv2_unpatchify.argtypes = [_vp, _vp] + [_i32] * 10 + [_vp]
+for _f in ("mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention", "mdv2_temporal_attention", "mdv2_patchify",
+           "mdv2_unpatchify"):
+    getattr(_lib, _f).restype = _i32
+
+EXPORTS = ("mdv2_version", "mdv2_last_error", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention",
+           "mdv2_temporal_attention", "mdv2_patchify", "mdv2_unpatchify")
+
+# kernel-launch counter (bench.py reports it as gpu_launches); +1 per C-ABI call that launches
+launches = 0
+default_backend = _BACKENDS[os.environ.get("MDV2_BACKEND", "auto")]
+
+
+def version() -> int:
+    return _lib.mdv2_version()
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return 0
+    if t.dtype == torch.bfloat16:
+        return 1
+    raise TypeError(f"libmdv2 supports fp32 and bf16 tensors, got {t.dtype}")
+
+
+def _ptr(t, dtype=None):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("libmdv2 ops need CUDA tensors (there is no CPU fallback)")
+    if dtype is not None and t.dtype != dtype:
+        raise TypeError(f"expected {dtype}, got {t.dtype}")
+    return t.data_ptr()
+
+
+def _rows2d(t: torch.Tensor):
+    """(ptr, leading dimension) of a 2-D view whose last dim is contiguous."""
+    assert t.dim() == 2 and (t.stride(1) == 1 or t.shape[1] == 1), "need a row-major 2-D view"
+    return _ptr(t), t.stride(0)
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _check(rc: int, name: str):
+    global launches
+    if rc != 0:
+        raise RuntimeError(f"{name} failed ({rc}): {_lib.mdv2_last_error().decode()}")
+    launches += 1
+
+
+def ln_modulate(x, out, mod, k_shift, k_scale, geo, eps=1e-6):
+    T, S, NC = geo
+    N, C = x.shape
+    assert x.is_contiguous() and out.is_contiguous() and mod.is_contiguous() and mod.dtype == torch.float32
+    assert mod.shape[-1] == C and out.shape == x.shape and out.dtype == x.dtype
+    _check(_lib.mdv2_ln_modulate(_ptr(x), _ptr(out), _ptr(mod), N, C, mod.shape[-2], k_shift, k_scale, T, S, NC,
+                                 eps, _dt(x), _stream()), "mdv2_ln_modulate")
+    return out
+
+
+def gemm(a, w, bias, out, geo=None, act=None, bias_scale=1.0, gate=None, res=None, res_map=None, rms=None,
+         backend=None):
+    M, K = a.shape
+    N = w.shape[0]
+    assert w.shape[1] == K and out.shape == (M, N) and a.dtype == w.dtype == out.dtype
+    pa, lda = _rows2d(a)
+    pw, ldw = _rows2d(w)
+    po, ldo = _rows2d(out)
+    T, S, NC = geo if geo is not None else (1, 1, 1)
+    gm, modK, kg = None, 0, 0
+    if gate is not None:
+        mod, kg = gate
+        assert mod.dtype == torch.float32 and mod.is_contiguous() and mod.shape[-1] == N and geo is not None
+        gm, modK = _ptr(mod), mod.shape[-2]
+    pr, ldr, rmod, rdiv = None, 0, 0, 0
+    if res is not None:
+        assert res.dtype == a.dtype and res.shape[1] == N
+        pr, ldr = _rows2d(res)
+        if res_map is not None:
+            rmod, rdiv = res_map
+        else:
+            assert res.shape[0] == M
+    qw = kw = None
+    hd = nq = nk = 0
+    if rms is not None and rms[0] is not None:
+        qw_t, kw_t, hd, nq, nk = rms
+        qw, kw = _ptr(qw_t, a.dtype), _ptr(kw_t, a.dtype)
+    be = default_backend if backend is None else _BACKENDS[backend]
+    _check(_lib.mdv2_gemm(pa, lda, pw, ldw, _ptr(bias, a.dtype) if bias is not None else None, po, ldo, M, N, K,
+                          1 if act == "gelu" else 0, float(bias_scale), gm, modK, kg, pr, ldr, rmod, rdiv, T, S, NC,
+                          qw, kw, hd, nq, nk, 1e-6, _dt(a), be, _stream()), "mdv2_gemm")
+    return out
+
+
+def attention(q, k, v, out, n_seq, Lq, Lk, H, D, scale, kv_map=None, backend=None):
+    pq, ldq = _rows2d(q)
+    pk, ldk = _rows2d(k)
+    pv, ldv = _rows2d(v)
+    po, ldo = _rows2d(out)
+    assert q.shape[0] == n_seq * Lq and q.shape[1] == H * D and out.shape == q.shape
+    assert k.shape[1] == H * D and v.shape == k.shape and k.shape[0] % Lk == 0
+    n_sets, pm = 1, None
+    if kv_map is not None:
+        assert kv_map.dtype == torch.int32 and kv_map.is_contiguous() and kv_map.shape[0] == n_seq
+        n_sets, pm = kv_map.shape[1], _ptr(kv_map)
+    be = default_backend if backend is None else _BACKENDS[backend]
+    _check(_lib.mdv2_attention(pq, ldq, pk, ldk, pv, ldv, po, ldo, n_seq, Lq, Lk, H, D, float(scale), pm, n_sets,
+                               _dt(q), be, _stream()), "mdv2_attention")
+    return out
+
+
+def temporal_attention(qkv, cos, sin, out, B, T, S, H, D, scale):
+    pq, ld = _rows2d(qkv)
+    po, ldo = _rows2d(out)
+    assert qkv.shape == (B * T * S, 3 * H * D) and out.shape == (B * T * S, H * D)
+    assert cos.dtype == torch.float32 and cos.is_contiguous() and cos.shape == (T, D) and sin.shape == (T, D)
+    _check(_lib.mdv2_temporal_attention(pq, ld, _ptr(cos), _ptr(sin), po, ldo, B, T, S, H, D, float(scale),
+                                        _dt(qkv), _stream()), "mdv2_temporal_attention")
+    return out
+
+
+def patchify(x5d, out, NCi, Hp, Wp, s0, Sl):
+    Bx, CN, T, Hx, Wx = x5d.shape
+    Cin = CN // NCi
+    assert x5d.is_contiguous() and out.is_contiguous() and out.dtype == x5d.dtype
+    assert out.shape == (Bx * NCi * T * Sl, Cin * 4)
+    _check(_lib.mdv2_patchify(_ptr(x5d), _ptr(out), Bx, Cin, NCi, T, Hx, Wx, Hp, Wp, s0, Sl, _dt(x5d), _stream()),
+           "mdv2_patchify")
+    return out
+
+
+def unpatchify(yo, out, NC, T, Hp, Wp):
+    b, CN, Tx, Hx, Wx = out.shape
+    Co = CN // NC
+    assert yo.is_contiguous() and out.is_contiguous() and out.dtype == torch.float32
+    assert yo.shape == (b * NC * T * Hp * Wp, 4 * Co)
+    _check(_lib.mdv2_unpatchify(_ptr(yo), _ptr(out), b, NC, Co, T, Hp, Wp, Tx, Hx, Wx, _dt(yo), _stream()),
+           "mdv2_unpatchify")
+    return out

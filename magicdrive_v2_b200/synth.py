@@ -65,7 +65,7 @@ WORKLOADS = {
                                caption_channels=64, model_max_length=24, map_size=400),
                     b=1, NC=6, t_pix=9, height=224, width=400, n_box=4, n_text=9),
     # tiny but with D=72 heads like XL (exercises the padded-head kernels)
-    "tiny_d72": dict(model=dict(hidden_size=288, depth=2, num_heads=4, control_depth=1,
+    "tiny_d72": dict(model=dict(hidden_size=576, depth=2, num_heads=8, control_depth=1,
                                 caption_channels=64, model_max_length=24, map_size=400),
                      b=2, NC=6, t_pix=9, height=224, width=400, n_box=4, n_text=9),
     # cfg2: XL/2, 6 views x 17 frames x 224x400, CFG batch-doubled (b=2)

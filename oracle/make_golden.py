@@ -35,10 +35,10 @@ def main():
         with torch.no_grad():
             out = ref(**inp)
             # bf16 run of the reference itself: its own low-precision gap
-            ref_bf = ref.to(torch.bfloat16)
+            import copy
+            ref_bf = copy.deepcopy(ref).to(torch.bfloat16)      # copy: .to() would round rope.freqs in place
             out_bf = ref_bf(**synth.to_device(inp, "cpu", torch.bfloat16))
-            ref.to(torch.float32)
-            synth.fill_params(ref, seed=0)     # restore exact fp32 weights after the bf16 round trip
+            del ref_bf
         fix = dict(workload=wl_name, x_mask=xm, seed=0, out=out.clone(),
                    ref_bf16_rel_l2=((out_bf - out).norm() / out.norm()).item(),
                    n_state=len(ref.state_dict()),
