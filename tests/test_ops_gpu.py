@@ -1,0 +1,187 @@
+"""GPU parity tests, kernel by kernel: every libmdv2 entry point (through the C ABI / ctypes) against
+its torch fp32 specification (tests/spec_ops.py) on the same seeded inputs.
+Tolerances: fp32 kernels 1e-5 relative L2 (different summation order only); bf16 kernels 6e-3
+(inputs/outputs rounded to bf16, fp32 accumulation)."""
+import pytest
+import torch
+
+import spec_ops
+from helpers import rel_l2
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+TOL = {torch.float32: 1e-5, torch.bfloat16: 6e-3}
+
+
+def ops():
+    from magicdrive_v2_b200 import ops as o
+    return o
+
+
+def rnd(*shape, dtype=torch.float32, seed=0, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(dtype).to(DEV)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("C", [384, 1152])
+def test_ln_modulate(dtype, C):
+    b, NC, T, S = 2, 3, 2, 37
+    N = b * NC * T * S
+    x = rnd(N, C, dtype=dtype, seed=1, scale=3.0) + 0.5
+    mod = rnd(b * T, 6, C, seed=2, scale=0.3)
+    out, ref = torch.empty_like(x), torch.empty_like(x)
+    ops().ln_modulate(x, out, mod, 3, 4, (T, S, NC))
+    spec_ops.ln_modulate(x, ref, mod, 3, 4, (T, S, NC))
+    assert rel_l2(out, ref) < TOL[dtype]
+
+
+def _gemm_case(dtype, M, N, K, backend, *, bias=True, act=None, gate=False, res=False, res_map=None, rms=None,
+               bias_scale=1.0, geo=(2, 37, 3), seed=0):
+    a = rnd(M, K, dtype=dtype, seed=seed + 1)
+    w = rnd(N, K, dtype=dtype, seed=seed + 2, scale=K ** -0.5)
+    bia = rnd(N, dtype=dtype, seed=seed + 3, scale=0.1) if bias else None
+    T, S, NC = geo
+    nb = -(-M // (S * T * NC))
+    mod = rnd(nb * T, 6, N, seed=seed + 4, scale=0.5) if gate else None
+    r = None
+    if res:
+        rows = M if res_map is None else (res_map[0] * (-(-M // (res_map[0] * res_map[1])) if res_map[1] else 1))
+        r = rnd(rows, N, dtype=dtype, seed=seed + 5)
+    rm = None
+    if rms is not None:
+        D, nq, nk = rms
+        rm = (1 + rnd(D, dtype=dtype, seed=seed + 6, scale=0.1), 1 + rnd(D, dtype=dtype, seed=seed + 7, scale=0.1), D, nq, nk)
+    kw = dict(geo=geo, act=act, bias_scale=bias_scale, gate=(mod, 2) if gate else None, res=r, res_map=res_map, rms=rm)
+    out = torch.full((M, N), float("nan"), dtype=dtype, device=DEV)
+    ref = torch.empty(M, N, dtype=dtype, device=DEV)
+    ops().gemm(a, w, bia, out, backend=backend, **kw)
+    spec_ops.gemm(a, w, bia, ref, **kw)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all()
+    return rel_l2(out, ref)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gemm_simt_epilogues(dtype):
+    tol = TOL[dtype]
+    assert _gemm_case(dtype, 300, 96, 80, "simt") < tol
+    assert _gemm_case(dtype, 444, 128, 64, "simt", act="gelu") < tol
+    assert _gemm_case(dtype, 444, 128, 64, "simt", gate=True, res=True) < tol
+    assert _gemm_case(dtype, 444, 128, 64, "simt", bias_scale=2.0, gate=True) < tol
+    assert _gemm_case(dtype, 444, 128, 64, "simt", res=True, res_map=(37, 0)) < tol
+    assert _gemm_case(dtype, 444, 128, 64, "simt", res=True, res_map=(74, 3)) < tol
+    assert _gemm_case(dtype, 222, 3 * 144, 64, "simt", rms=(72, 144, 144)) < tol
+    assert _gemm_case(dtype, 222, 192, 64, "simt", bias=False, rms=(64, 64, 64)) < tol
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (128, 256, 128), (300, 192, 256), (1000, 1152, 1152),
+                                   (24000, 1152, 1152), (777, 4608, 1152), (513, 1152, 4608), (200, 64, 1152),
+                                   (5000, 384, 64)])
+def test_gemm_tcgen05_plain(M, N, K):
+    assert _gemm_case(torch.bfloat16, M, N, K, "tcgen05") < TOL[torch.bfloat16]
+
+
+def test_gemm_tcgen05_epilogues():
+    tol = TOL[torch.bfloat16]
+    bf = torch.bfloat16
+    assert _gemm_case(bf, 1000, 1152, 1152, "tcgen05", act="gelu") < tol
+    assert _gemm_case(bf, 1000, 1152, 1152, "tcgen05", gate=True, res=True) < tol
+    assert _gemm_case(bf, 1000, 1152, 1152, "tcgen05", bias_scale=2.0, gate=True) < tol
+    assert _gemm_case(bf, 1000, 1152, 64, "tcgen05", res=True, res_map=(37, 0)) < tol
+    assert _gemm_case(bf, 1000, 1152, 64, "tcgen05", res=True, res_map=(74, 3)) < tol
+    assert _gemm_case(bf, 1000, 3456, 1152, "tcgen05", rms=(72, 1152, 1152)) < tol
+    assert _gemm_case(bf, 1000, 3456, 1152, "tcgen05", bias=False, rms=(72, 1152, 1152)) < tol
+    assert _gemm_case(bf, 700, 1152, 384, "tcgen05", rms=(64, 384, 384)) < tol
+
+
+def test_gemm_tcgen05_in_place_residual_and_strided_views():
+    bf = torch.bfloat16
+    M, C = 900, 1152
+    x = rnd(M, C, dtype=bf, seed=1)
+    a = rnd(M, C, dtype=bf, seed=2)
+    w = rnd(C, C, dtype=bf, seed=3, scale=C ** -0.5)
+    ref = torch.empty_like(x)
+    spec_ops.gemm(a, w, None, ref, res=x)
+    ops().gemm(a, w, None, x, res=x, backend="tcgen05")            # out aliases res
+    assert rel_l2(x, ref) < TOL[bf]
+    # A operand = column slice of a wider buffer (lda > K); out = column slice too
+    wide = rnd(M, 3 * C, dtype=bf, seed=4)
+    out_w = torch.zeros(M, 2 * C, dtype=bf, device=DEV)
+    ref2 = torch.empty(M, C, dtype=bf, device=DEV)
+    spec_ops.gemm(wide[:, C:2 * C], w, None, ref2)
+    ops().gemm(wide[:, C:2 * C], w, None, out_w[:, C:], backend="tcgen05")
+    assert rel_l2(out_w[:, C:], ref2) < TOL[bf]
+    assert out_w[:, :C].abs().max() == 0
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("D", [64, 72])
+def test_attention_simt(dtype, D):
+    n_seq, Lq, Lk, H = 12, 150, 150, 4
+    qkv = rnd(n_seq * Lq, 3 * H * D, dtype=dtype, seed=1)
+    C = H * D
+    q, k, v = qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:]
+    out, ref = (torch.empty(n_seq * Lq, C, dtype=dtype, device=DEV) for _ in range(2))
+    tol = 3 * TOL[dtype]
+    ops().attention(q, k, v, out, n_seq, Lq, Lk, H, D, D ** -0.5, backend="simt")
+    spec_ops.attention(q, k, v, ref, n_seq, Lq, Lk, H, D, D ** -0.5)
+    assert rel_l2(out, ref) < tol
+    # cross-view: two neighbour K/V sets summed
+    kv_map = torch.stack([(torch.arange(n_seq) + 1) % n_seq, (torch.arange(n_seq) + 5) % n_seq], 1).int().to(DEV)
+    ops().attention(q, k, v, out, n_seq, Lq, Lk, H, D, D ** -0.5, kv_map=kv_map.contiguous(), backend="simt")
+    spec_ops.attention(q, k, v, ref, n_seq, Lq, Lk, H, D, D ** -0.5, kv_map=kv_map)
+    assert rel_l2(out, ref) < tol
+    # cross-attention: short ragged K/V
+    Lc = 23
+    kv = rnd(n_seq * Lc, 2 * C, dtype=dtype, seed=2)
+    ops().attention(q, kv[:, :C], kv[:, C:], out, n_seq, Lq, Lc, H, D, D ** -0.5, backend="simt")
+    spec_ops.attention(q, kv[:, :C], kv[:, C:], ref, n_seq, Lq, Lc, H, D, D ** -0.5)
+    assert rel_l2(out, ref) < tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("T,D", [(1, 64), (3, 64), (5, 72), (17, 72)])
+def test_temporal_attention(dtype, T, D):
+    B, S, H = 3, 41, 4
+    qkv = rnd(B * T * S, 3 * H * D, dtype=dtype, seed=1)
+    ang = torch.arange(T, dtype=torch.float32)[:, None] * (1.0 / 10000 ** (torch.arange(0, D, 2).float() / D))[None]
+    ang = ang.repeat_interleave(2, dim=-1).to(DEV)
+    cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
+    out, ref = (torch.empty(B * T * S, H * D, dtype=dtype, device=DEV) for _ in range(2))
+    ops().temporal_attention(qkv, cos, sin, out, B, T, S, H, D, D ** -0.5)
+    spec_ops.temporal_attention(qkv, cos, sin, ref, B, T, S, H, D, D ** -0.5)
+    assert rel_l2(out, ref) < 2 * TOL[dtype]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_patchify_unpatchify_bit_exact(dtype):
+    b, NC, Cin, T, Hx, Wx, Hp, Wp = 2, 3, 4, 2, 7, 10, 5, 5
+    x = rnd(b, Cin * NC, T, Hx, Wx, dtype=dtype, seed=1)
+    S = Hp * Wp
+    for s0, Sl in ((0, S), (10, 5)):
+        out = torch.empty(b * NC * T * Sl, Cin * 4, dtype=dtype, device=DEV)
+        ref = torch.empty_like(out)
+        ops().patchify(x, out, NC, Hp, Wp, s0, Sl)
+        spec_ops.patchify(x, ref, NC, Hp, Wp, s0, Sl)
+        assert torch.equal(out, ref)                              # pure index map: bit-exact
+    y = rnd(b * NC * T * S, 4 * Cin, dtype=dtype, seed=2)
+    o = torch.empty(b, Cin * NC, T, Hx, Wx, dtype=torch.float32, device=DEV)
+    r = torch.empty_like(o)
+    ops().unpatchify(y, o, NC, T, Hp, Wp)
+    spec_ops.unpatchify(y, r, NC, T, Hp, Wp)
+    assert torch.equal(o, r)
+
+
+def test_error_behaviour():
+    o = ops()
+    x = rnd(8, 20, dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError):                              # C not a multiple of the vector width
+        o.ln_modulate(x[:, :12].contiguous(), torch.empty(8, 12, dtype=torch.bfloat16, device=DEV),
+                      torch.zeros(1, 2, 12, device=DEV), 0, 1, (1, 8, 1))
+    with pytest.raises(RuntimeError):                              # shape the tcgen05 kernel does not tile
+        o.gemm(rnd(8, 20, dtype=torch.bfloat16), rnd(24, 20, dtype=torch.bfloat16), None,
+               torch.empty(8, 24, dtype=torch.bfloat16, device=DEV), backend="tcgen05")
+    # empty input is a no-op
+    e = torch.empty(0, 64, dtype=torch.bfloat16, device=DEV)
+    o.gemm(e, rnd(64, 64, dtype=torch.bfloat16), None, torch.empty(0, 64, dtype=torch.bfloat16, device=DEV))

@@ -1,0 +1,36 @@
+"""Micro-benchmark of the libmdv2 GEMM on the STDiT3-XL shapes (CUDA events, L2-cold rotation)."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from magicdrive_v2_b200 import ops
+
+def bench(M, N, K, iters=20, **kw):
+    bf = torch.bfloat16
+    nbuf = max(2, int(300e6 // (M * K * 2 + M * N * 2)) + 1)
+    a = [torch.randn(M, K, device="cuda", dtype=bf) for _ in range(nbuf)]
+    o = [torch.empty(M, N, device="cuda", dtype=bf) for _ in range(nbuf)]
+    w = torch.randn(N, K, device="cuda", dtype=bf) * K ** -0.5
+    b = torch.randn(N, device="cuda", dtype=bf)
+    for i in range(3):
+        ops.gemm(a[i % nbuf], w, b, o[i % nbuf], **kw)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters):
+        ops.gemm(a[i % nbuf], w, b, o[i % nbuf], **kw)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    tf = 2.0 * M * N * K / ms / 1e9
+    # cuBLAS yard-stick
+    for i in range(3): torch.matmul(a[i % nbuf], w.t())
+    e0.record()
+    for i in range(iters): torch.matmul(a[i % nbuf], w.t())
+    e1.record(); torch.cuda.synchronize()
+    ms2 = e0.elapsed_time(e1) / iters
+    print(f"M={M:7d} N={N:5d} K={K:5d}  mdv2 {ms:8.3f} ms {tf:7.1f} TF   cublas {ms2:8.3f} ms {2.0*M*N*K/ms2/1e9:7.1f} TF", flush=True)
+
+if __name__ == "__main__":
+    for M in (24000, 336000 // 4):
+        for (N, K) in ((1152, 1152), (3456, 1152), (4608, 1152), (1152, 4608), (2304, 1152)):
+            bench(M, N, K, backend="tcgen05")
+    bench(24000, 4608, 1152, backend="tcgen05", act="gelu")
