@@ -16,7 +16,8 @@ using namespace sm100;
 namespace {
 constexpr int BM = 128, BK = 64;
 constexpr int A_BYTES = BM * BK * 2;
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_EPI_WARPS = 8;                      // 2 per TMEM lane quarter, interleaved over column chunks
+constexpr int NUM_THREADS = 64 + NUM_EPI_WARPS * 32;
 constexpr int TMEM_COLS = 512, ACC_STRIDE = 256;
 
 template <int BN, int HD>
@@ -24,9 +25,9 @@ struct Cfg {
   static constexpr int CW = HD ? HD : 64;                // epilogue chunk width (columns)
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int PITCH = CW * 2 + 32 - ((CW * 2) % 32) + 16;   // odd multiple of 16 B
-  static constexpr int ROWINFO = 4 * 32 * 16;                          // per-row gate / residual row cache
-  static constexpr int STAGING = 4 * 32 * PITCH + ROWINFO;
+  static constexpr int PITCH = ((CW * 2 / 16) % 2 == 1) ? CW * 2 : CW * 2 + 16;   // odd multiple of 16 B
+  static constexpr int EPW = 32 * PITCH + 512 + 320;       // per warp: staging + row info + bias (fp32)
+  static constexpr int STAGING = NUM_EPI_WARPS * EPW;
   static constexpr int STAGES_RAW = (232448 - 1024 - 256 - STAGING) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
   static constexpr int SMEM = STAGES * STAGE_BYTES + STAGING + 256 + 1024;  // + barriers + align slack
@@ -77,7 +78,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], 4);
+      mbar_init(&tempty[i], NUM_EPI_WARPS);
     }
     fence_mbar_init();
   }
@@ -132,96 +133,112 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
     }
   } else {
-    // ===== epilogue warps (TMEM lane quarter = warp % 4) =====
+    // ===== epilogue warps: TMEM lane quarter = warp % 4, column chunks ch ≡ half (mod 2) =====
     constexpr int CW = C::CW;
+    constexpr int UPR = CW / 8;                       // 16-byte units per staged row
     const int quarter = warp & 3;
-    uint8_t* stg = staging + quarter * 32 * C::PITCH;
-    int64_t* row_res = reinterpret_cast<int64_t*>(staging + 4 * 32 * C::PITCH) + quarter * 64;
+    const int half = (warp - 2) >> 2;
+    uint8_t* stg = staging + (warp - 2) * C::EPW;
+    int64_t* row_res = reinterpret_cast<int64_t*>(stg + 32 * C::PITCH);
     int64_t* row_gate = row_res + 32;
+    float* sbias = reinterpret_cast<float*>(row_gate + 32);
     int acc = 0;
     uint32_t acc_phase = 0;
     const Epilogue<bf16>& ep = p.ep;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
       const int64_t m0 = (tile / n_tiles_n) * BM;
       const int n0 = (int)(tile % n_tiles_n) * BN;
-      mbar_wait(&tfull[acc], acc_phase);
-      tc_fence_after();
-      const uint32_t t_row = tmem_base + acc * ACC_STRIDE + ((uint32_t)(quarter * 32) << 16);
       {  // per-row epilogue context, once per tile (64-bit divisions stay out of the inner loops)
         const int64_t gr = m0 + quarter * 32 + lane;
         const RowCtx rc = ep.row_ctx(gr < p.M ? gr : 0);
         row_res[lane] = rc.res_row * ep.ldr;
         row_gate[lane] = rc.gate ? (int64_t)(rc.gate - ep.gate_mod) : -1;
-        __syncwarp();
       }
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + acc * ACC_STRIDE + ((uint32_t)(quarter * 32) << 16);
 #pragma unroll 1
-      for (int ch = 0; ch < BN / CW; ++ch) {
+      for (int ch = half; ch < BN / CW; ch += 2) {
         const int c0 = n0 + ch * CW;
         uint32_t raw[CW];
         tmem_ld_x32(t_row + ch * CW, raw);
         tmem_ld_x32(t_row + ch * CW + 32, raw + 32);
         if constexpr (CW == 72) tmem_ld_x8(t_row + ch * CW + 64, raw + 64);
+        // bias of this chunk -> smem (fp32) while the TMEM load is in flight
+        for (int jj = lane; jj < CW; jj += 32)
+          sbias[jj] = ep.bias ? ep.bias_scale * __bfloat162float(ep.bias[c0 + jj]) : 0.f;
+        __syncwarp();
         tmem_ld_wait();
         float v[CW];
 #pragma unroll
-        for (int j = 0; j < CW; ++j) v[j] = __uint_as_float(raw[j]);
-        if (ep.bias) {
-#pragma unroll
-          for (int j = 0; j < CW; ++j) v[j] += ep.bias_scale * __bfloat162float(__ldg(ep.bias + c0 + j));
+        for (int jj = 0; jj < CW; jj += 4) {
+          const float4 b4 = *reinterpret_cast<const float4*>(sbias + jj);
+          v[jj + 0] = __uint_as_float(raw[jj + 0]) + b4.x;
+          v[jj + 1] = __uint_as_float(raw[jj + 1]) + b4.y;
+          v[jj + 2] = __uint_as_float(raw[jj + 2]) + b4.z;
+          v[jj + 3] = __uint_as_float(raw[jj + 3]) + b4.w;
         }
         if constexpr (HD != 0) {
           const bf16* w = c0 < p.n_q ? p.rms_q : (c0 < p.n_q + p.n_k ? p.rms_k : nullptr);
           if (w != nullptr) {
             float ss = 0.f;
 #pragma unroll
-            for (int j = 0; j < CW; ++j) ss += v[j] * v[j];
+            for (int jj = 0; jj < CW; ++jj) ss += v[jj] * v[jj];
             const float r = rsqrtf(ss / CW + p.eps);
 #pragma unroll
-            for (int j = 0; j < CW; ++j)
-              v[j] = __bfloat162float(__ldg(w + j)) * __bfloat162float(__float2bfloat16_rn(v[j] * r));
+            for (int jj = 0; jj < CW; ++jj)
+              v[jj] = __bfloat162float(__ldg(w + jj)) * __bfloat162float(__float2bfloat16_rn(v[jj] * r));
           }
         }
         if (ep.act == 1) {
 #pragma unroll
-          for (int j = 0; j < CW; ++j) v[j] = gelu_tanh(v[j]);
+          for (int jj = 0; jj < CW; ++jj) v[jj] = gelu_tanh_fast(v[jj]);
         }
-        // row phase -> staging (bf16 when no gate/residual follows, else keep bf16 too: the
-        // reference rounds the projection output to bf16 before gate/residual as well)
+        // row phase -> staging (bf16, like the reference rounds a projection before gate/residual)
         uint8_t* srow = stg + lane * C::PITCH;
 #pragma unroll
-        for (int j = 0; j < CW; j += 8) {
+        for (int jj = 0; jj < CW; jj += 8) {
           Vec16<bf16> pk;
-          pk.pack(v + j);
-          *reinterpret_cast<uint4*>(srow + j * 2) = pk.raw;
+          pk.pack(v + jj);
+          *reinterpret_cast<uint4*>(srow + jj * 2) = pk.raw;
         }
         __syncwarp();
-        // column phase: coalesced 4-byte accesses, gate / residual / store
-        constexpr int WPR = CW / 2;  // 32-bit words per row
-#pragma unroll 4
-        for (int idx = lane; idx < 32 * WPR; idx += 32) {
-          const int rl = idx / WPR, wd = idx % WPR;
+        // column phase: coalesced 16-byte accesses: gate / residual / store
+#pragma unroll 2
+        for (int idx = lane; idx < 32 * UPR; idx += 32) {
+          const int rl = idx / UPR, u = idx % UPR;
           const int64_t gr = m0 + quarter * 32 + rl;
           if (gr < p.M) {
-            float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(stg + rl * C::PITCH + wd * 4));
-            const int col = c0 + wd * 2;
+            Vec16<bf16> pk;
+            pk.raw = *reinterpret_cast<const uint4*>(stg + rl * C::PITCH + u * 16);
+            const int col = c0 + u * 8;
             const int64_t goff = row_gate[rl];
-            if (goff >= 0) {
-              const float2 g = *reinterpret_cast<const float2*>(ep.gate_mod + goff + col);
-              f.x *= g.x;
-              f.y *= g.y;
+            if (goff >= 0 || ep.res) {
+              float f[8];
+              pk.unpack(f);
+              if (goff >= 0) {
+                const float4 g0 = *reinterpret_cast<const float4*>(ep.gate_mod + goff + col);
+                const float4 g1 = *reinterpret_cast<const float4*>(ep.gate_mod + goff + col + 4);
+                f[0] *= g0.x; f[1] *= g0.y; f[2] *= g0.z; f[3] *= g0.w;
+                f[4] *= g1.x; f[5] *= g1.y; f[6] *= g1.z; f[7] *= g1.w;
+              }
+              if (ep.res) {
+                Vec16<bf16> rv;
+                rv.raw = *reinterpret_cast<const uint4*>(ep.res + row_res[rl] + col);
+                float rf[8];
+                rv.unpack(rf);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) f[e] += rf[e];
+              }
+              pk.pack(f);
             }
-            if (ep.res) {
-              const float2 rr = __bfloat1622float2(
-                  *reinterpret_cast<const __nv_bfloat162*>(ep.res + row_res[rl] + col));
-              f.x += rr.x;
-              f.y += rr.y;
-            }
-            *reinterpret_cast<__nv_bfloat162*>(p.out + gr * p.ldo + col) = __floats2bfloat162_rn(f.x, f.y);
+            *reinterpret_cast<uint4*>(p.out + gr * p.ldo + col) = pk.raw;
           }
         }
         __syncwarp();
       }
       tc_fence_before();
+      __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
@@ -275,6 +292,30 @@ int mdv2_make_tmap_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t
   return MDV2_OK;
 }
 
+// 3-D bf16 view (d, head, row) of a row-major activation whose heads are D-wide column groups:
+// box = 64 x 1 x box_rows, SW128; columns beyond D are zero-filled by the TMA unit.
+int mdv2_make_tmap_3d_heads(CUtensorMap* out, const void* ptr, uint64_t rows, uint32_t H, uint32_t D, uint64_t ld,
+                            uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    mdv2_set_error("cuTensorMapEncodeTiled unavailable");
+    return MDV2_ECUDA;
+  }
+  cuuint64_t dims[3] = {D, H, rows};
+  cuuint64_t strides[2] = {(cuuint64_t)D * 2, ld * 2};
+  cuuint32_t box[3] = {64, 1, box_rows};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    mdv2_set_error("cuTensorMapEncodeTiled(3d) failed (%d) ptr=%p rows=%llu H=%u D=%u ld=%llu", (int)r, ptr,
+                   (unsigned long long)rows, H, D, (unsigned long long)ld);
+    return MDV2_ECUDA;
+  }
+  return MDV2_OK;
+}
+
 namespace {
 template <int BN, int HD>
 int launch(const CUtensorMap& ta, const CUtensorMap& tw, const Params& p, cudaStream_t st) {
@@ -311,7 +352,7 @@ int pick_bn(int N, const RmsArgs* rms) {
 
 bool mdv2_gemm_sm100_supported(int64_t M, int N, int K, int64_t lda, int64_t ldw, int64_t ldo, const RmsArgs* rms) {
   if (M <= 0 || K % BK != 0 || K <= 0) return false;
-  if (lda % 8 != 0 || ldw % 8 != 0 || ldo % 2 != 0) return false;
+  if (lda % 8 != 0 || ldw % 8 != 0 || ldo % 8 != 0 || N % 8 != 0) return false;
   if (rms && rms->wq && (rms->n_q % rms->head_dim != 0 || rms->n_k % rms->head_dim != 0)) return false;
   return pick_bn(N, rms) != 0;
 }
@@ -320,7 +361,8 @@ int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void
                     int K, const Epilogue<bf16>& ep, const RmsArgs* rms, cudaStream_t st) {
   MDV2_REQUIRE(mdv2_gemm_sm100_supported(M, N, K, lda, ldw, ldo, rms), "gemm_sm100: unsupported shape M=%lld N=%d K=%d",
                (long long)M, N, K);
-  MDV2_REQUIRE(((uintptr_t)a % 16 == 0) && ((uintptr_t)w % 16 == 0) && ((uintptr_t)out % 4 == 0),
+  MDV2_REQUIRE(((uintptr_t)a % 16 == 0) && ((uintptr_t)w % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
+                   (!ep.res || ((uintptr_t)ep.res % 16 == 0 && ep.ldr % 8 == 0)),
                "gemm_sm100: operands must be 16-byte aligned");
   const int bn = pick_bn(N, rms);
   CUtensorMap ta, tw;

@@ -322,6 +322,13 @@ class MagicDriveSTDiT3(PreTrainedModel):
         if self.cache_conditions and self._cond_cache is not None and self._cond_cache[0] == key:
             return self._cond_cache[1]
         C = self.hidden_size
+
+        def cast(t):     # callers hand conditions in the model dtype (inference_magicdrive.py:345-358); be lenient
+            return t.to(dtype) if isinstance(t, torch.Tensor) and t.is_floating_point() else t
+        cams, rel_pos, maps = cast(cams), cast(rel_pos), cast(maps)
+        drop_cond_mask, drop_frame_mask = cast(drop_cond_mask), cast(drop_frame_mask)
+        if bbox is not None:
+            bbox = {k_: cast(v_) for k_, v_ in bbox.items()}
         tf32 = contextlib.nullcontext()
         if dtype == torch.float32 and y.is_cuda:
             tf32 = torch.backends.cudnn.flags(enabled=True, allow_tf32=False)

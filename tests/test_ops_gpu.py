@@ -185,3 +185,44 @@ def test_error_behaviour():
     # empty input is a no-op
     e = torch.empty(0, 64, dtype=torch.bfloat16, device=DEV)
     o.gemm(e, rnd(64, 64, dtype=torch.bfloat16), None, torch.empty(0, 64, dtype=torch.bfloat16, device=DEV))
+
+
+def _attn_case(n_seq, Lq, Lk, H, D, *, kv="self", seed=0):
+    bf = torch.bfloat16
+    C = H * D
+    qkv = rnd(n_seq * Lq, 3 * C, dtype=bf, seed=seed + 1)
+    q = qkv[:, :C]
+    kv_map = None
+    if kv == "cross":
+        kvb = rnd(n_seq * Lk, 2 * C, dtype=bf, seed=seed + 2)
+        k, v = kvb[:, :C], kvb[:, C:]
+    else:
+        assert Lq == Lk
+        k, v = qkv[:, C:2 * C], qkv[:, 2 * C:]
+        if kv == "xview":
+            kv_map = torch.stack([(torch.arange(n_seq) + 1) % n_seq, (torch.arange(n_seq) + n_seq - 1) % n_seq], 1)
+            kv_map = kv_map.int().contiguous().to(DEV)
+    out = torch.full((n_seq * Lq, C), float("nan"), dtype=bf, device=DEV)
+    ref = torch.empty(n_seq * Lq, C, dtype=bf, device=DEV)
+    ops().attention(q, k, v, out, n_seq, Lq, Lk, H, D, D ** -0.5, kv_map=kv_map, backend="tcgen05")
+    spec_ops.attention(q, k, v, ref, n_seq, Lq, Lk, H, D, D ** -0.5, kv_map=kv_map)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all()
+    return rel_l2(out, ref)
+
+
+@pytest.mark.parametrize("D", [64, 72])
+@pytest.mark.parametrize("L", [128, 256, 400, 77])
+def test_attention_tcgen05_self(D, L):
+    assert _attn_case(6, L, L, 4, D) < 2e-2
+
+
+@pytest.mark.parametrize("D", [64, 72])
+def test_attention_tcgen05_cross_view_and_cross(D):
+    assert _attn_case(6, 400, 400, 4, D, kv="xview") < 2e-2
+    assert _attn_case(6, 400, 62, 4, D, kv="cross") < 2e-2          # one ragged K/V tile
+    assert _attn_case(6, 350, 150, 4, D, kv="cross") < 2e-2         # two K/V tiles, ragged
+
+
+def test_attention_tcgen05_xl_shape():
+    assert _attn_case(12, 1400, 1400, 16, 72) < 2e-2
