@@ -1,0 +1,417 @@
+#!/usr/bin/env python
+"""bench.py — STDiT3 denoise steps/sec (device-timed) on N B200s of one node.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+A "step" is ONE forward of the 28-block MagicDriveSTDiT3-XL/2 denoiser on a CFG-batch-doubled (b=2)
+packed latent of 6 views x 17 pixel frames (5 latent frames), bf16, through the repo's drop-in
+nn.Module (magicdrive_v2_b200.stdit3) whose hot path is libmdv2.so (hand-written sm_100a kernels).
+Default workload = BASELINE.json's target configuration, 848x1600 (N = 336 000 tokens), at every N:
+N > 1 shards the spatial tokens over the ranks (Ulysses all-to-all, "scaling": "strong").
+The 224x400 configuration (configs[1]) is reported beside it at N = 1 under "secondary".
+
+Timed regions:
+  value : K forwards, inputs resident in HBM, condition encoders re-run every step (no cached
+          outputs), CUDA events bracketed by barrier + synchronize, max over ranks.
+  e2e   : the same forward called with HOST (pinned) inputs: H2D of every input tensor and D2H of the
+          predicted velocity inside the timed region.
+  roofline / kernels : one extra instrumented step with a CUDA-event pair around every libmdv2 call.
+  cpu_baseline : the CPU oracle (port of the reference forward, oracle/stdit3_oracle.py) on the host
+          cores, on a bounded sample of the same workload (rank 0, N = 1 only).
+`--impl reference` times only that CPU leg (the reference is pure PyTorch and cannot travel to the
+GPU box; its restatement, pinned to the reference's golden vectors, is what runs).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "STDiT3 denoise steps/sec (device-timed)"
+UNIT = "steps/s"
+N_BLOCKS = dict(base_blocks_s=28, control_blocks_s=13, base_blocks_t=28, control_blocks_t=13)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d["bf16_tflops_sustained"],
+                    source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback (B200_PROFILING.md)")
+
+
+def algorithmic_flops(b, NC, T, S, L, C=1152, depth=28, cdepth=13, mlp=4):
+    """2·MAC, de-duplicated cross-view, head_dim un-padded, condition embedders excluded."""
+    N = b * NC * T * S
+    per_tok = {  # C^2 MACs per token
+        "base_s": 3 + 1 + (1 + 1) + (3 + 1 + 1) + 2 * mlp,      # qkv, proj, cross q+proj, xview qkv+proj+mva, mlp
+        "ctrl_s": 3 + 1 + (1 + 1) + 2 * mlp + 1,                # + after_proj
+        "base_t": 3 + 1 + (1 + 1) + 2 * mlp,
+        "ctrl_t": 3 + 1 + (1 + 1) + 2 * mlp + 1,
+    }
+    lin = 2.0 * N * C * C * (depth * per_tok["base_s"] + cdepth * per_tok["ctrl_s"] + depth * per_tok["base_t"] +
+                             cdepth * per_tok["ctrl_t"])
+    seqs = b * NC * T
+    attn_s = 4.0 * seqs * S * S * C * (depth + cdepth)
+    attn_xv = 4.0 * seqs * S * S * C * 2 * depth
+    attn_c = 4.0 * seqs * S * L * C * 2 * (depth + cdepth)
+    attn_t = 4.0 * b * NC * S * T * T * C * (depth + cdepth)
+    return dict(total=lin + attn_s + attn_xv + attn_c + attn_t, linear=lin, spatial_attn=attn_s,
+                cross_view=attn_xv, cross_attn=attn_c, temporal=attn_t)
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU leg (oracle port), shared by cpu_baseline and --impl reference
+# ---------------------------------------------------------------------------------------------------
+class CpuSample:
+    """Bounded sample of the workload for the host cores: b = 1, ONE latent frame (t_pix = 1), ONE block of
+    each of the four kinds at the full XL width and the full per-frame token count S.  The full step is
+    estimated as  (b·T scale) x (other + sum_kind n_kind · t_kind)  — every stage is token-linear (spatial
+    attention per frame; temporal attention's T^2 term is < 0.1 % of the work)."""
+
+    def __init__(self, wl_name):
+        from magicdrive_v2_b200 import synth
+        from magicdrive_v2_b200.config import MagicDriveSTDiT3Config
+        from magicdrive_v2_b200.stdit3 import MagicDriveSTDiT3
+        wl = dict(synth.WORKLOADS[wl_name])
+        self.full_T = synth.latent_frames(wl["t_pix"])
+        self.full_b = wl["b"]
+        wl.update(b=1, t_pix=1)
+        kw = synth.model_kwargs(**dict(wl["model"], depth=1, control_depth=1))
+        torch.manual_seed(0)
+        model = MagicDriveSTDiT3(MagicDriveSTDiT3Config(**kw)).eval()     # container of reference-layout weights
+        synth.fill_params(model, seed=0)
+        self.sd = {k: v.clone() for k, v in model.state_dict().items()}
+        self.kw = kw
+        self.inp = synth.make_inputs(wl, seed=0, x_mask="ones", kw=kw)
+        self.desc = (f"oracle port, fp32: b=1 of {self.full_b}, 1 of {self.full_T} latent frames, 1 block of each "
+                     f"kind (base_s/ctrl_s/base_t/ctrl_t) of 28/13/28/13 at full width and S; step time = "
+                     f"{self.full_b * self.full_T} x (other + sum n_kind·t_kind)")
+
+    def step(self):
+        """-> estimated seconds for the FULL step on these host cores."""
+        from oracle import stdit3_oracle
+        timers = {}
+        t0 = time.perf_counter()
+        stdit3_oracle.forward(self.sd, self.kw, timers=timers, **self.inp)
+        total = time.perf_counter() - t0
+        blocks = sum(timers.values())
+        other = total - blocks
+        est = other + sum(N_BLOCKS[k] * timers.get(k, 0.0) for k in N_BLOCKS)
+        return est * self.full_b * self.full_T, total
+
+
+def run_reference_arm(args, rank):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sample = CpuSample(args.workload)
+    args.warmup = min(args.warmup, 1)        # one sample is ~30-60 s of host work; CPU needs no more warm-up
+    for _ in range(args.warmup):
+        sample.step()
+    ests, wall = [], 0.0
+    for _ in range(args.steps):
+        e, w = sample.step()
+        ests.append(e)
+        wall += w
+    est = sum(ests) / len(ests)
+    val = 1.0 / est
+    line = dict(metric=METRIC, value=val, unit=UNIT, impl="reference", n_gpus=args.gpus, steps=args.steps,
+                warmup=args.warmup, ms_per_step=est * 1e3, higher_is_better=True, scaling="strong",
+                vs_baseline=None, dtype="fp32", data="synthetic",
+                config=workload_config(args.workload, 1),
+                cpu_baseline=dict(value=val, unit=UNIT, cores=cores, kind="port", sample=sample.desc,
+                                  sample_wall_s=wall / max(1, args.steps)),
+                e2e=dict(value=val, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                gpu_launches=0)
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+def workload_config(name, p):
+    from magicdrive_v2_b200 import indexmaps, synth
+    wl = synth.WORKLOADS[name]
+    T = synth.latent_frames(wl["t_pix"])
+    Hp, Wp = -(-(-(-wl["height"] // 8)) // 2), -(-(-(-wl["width"] // 8)) // 2)
+    Hp += indexmaps.h_pad_for(Hp, Wp, 8)
+    S = Hp * Wp
+    return dict(workload=name, denoiser="MagicDriveSTDiT3-XL/2 (28+28 base, 13+13 control blocks, hidden 1152)",
+                views=wl["NC"], pixel_frames=wl["t_pix"], latent_frames=T, resolution=f"{wl['height']}x{wl['width']}",
+                cfg_batch=wl["b"], tokens_per_frame=S, tokens=wl["b"] * wl["NC"] * T * S,
+                parallelism=f"sp{p}" if p > 1 else "single",
+                l2_policy="activations per kernel (>= 96 MB at 224x400, 774 MB at 848x1600 per pass) exceed/rotate "
+                          "through L2; no explicit flush")
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.strip().split(", ") for r in open(self.f.name) if r.strip()]
+        os.unlink(self.f.name)
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for r in rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.strip().lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["no samples"])
+        return dict(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), power_w_max=max(pw), samples=len(sm),
+                    reasons=sorted(reasons))
+
+
+def build_model(wl_name, device, sp):
+    from magicdrive_v2_b200 import synth
+    from magicdrive_v2_b200.config import MagicDriveSTDiT3Config
+    from magicdrive_v2_b200.stdit3 import MagicDriveSTDiT3
+    wl = synth.WORKLOADS[wl_name]
+    kw = synth.model_kwargs(**dict(wl["model"], enable_sequence_parallelism=sp))
+    torch.manual_seed(0)
+    with torch.device(device):
+        model = MagicDriveSTDiT3(MagicDriveSTDiT3Config(**kw)).eval()
+    synth.fill_params(model, seed=0, on_device=True)       # same recipe as the parity tests, device RNG
+    model = model.to(device=device, dtype=torch.bfloat16)
+    return model, wl, kw
+
+
+def pin(obj):
+    if isinstance(obj, torch.Tensor):
+        return obj.pin_memory()
+    if isinstance(obj, dict):
+        return {k: pin(v) for k, v in obj.items()}
+    return obj
+
+
+def nbytes(obj):
+    if isinstance(obj, torch.Tensor):
+        return obj.numel() * obj.element_size()
+    if isinstance(obj, dict):
+        return sum(nbytes(v) for v in obj.values())
+    return 0
+
+
+def to_dev(obj, device):
+    if isinstance(obj, torch.Tensor):
+        return obj.to(device, non_blocking=True)
+    if isinstance(obj, dict):
+        return {k: to_dev(v, device) for k, v in obj.items()}
+    return obj
+
+
+def timed_steps(fn, steps, dist_on):
+    import torch.distributed as dist
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if dist_on:
+        dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    if dist_on:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return ms.item()
+
+
+def measure(wl_name, args, rank, world, device, pk, do_profile=True):
+    from magicdrive_v2_b200 import ops, synth
+    dist_on = world > 1
+    model, wl, kw = build_model(wl_name, device, sp=dist_on)
+    if dist_on:
+        import torch.distributed as dist
+        model.sp_group = dist.group.WORLD
+    host = pin(synth.make_inputs(wl, seed=0, x_mask="ones", kw=kw))
+    inp = to_dev(host, device)
+    torch.cuda.synchronize()
+    model.cache_conditions = False                  # every step re-runs the condition encoders
+
+    def step():
+        return model(**inp)
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    n0 = ops.launches
+    clk = ClockSampler(torch.cuda.current_device()) if rank == 0 else None
+    ms = timed_steps(step, args.steps, dist_on)
+    clocks = clk.stop() if clk else None
+    launches = ops.launches - n0
+    ms_step = ms / args.steps
+
+    # steady state of a sampling loop: condition encodings cached across steps
+    model.cache_conditions = True
+    step()
+    ms_cached = timed_steps(step, args.steps, dist_on) / args.steps
+    model.cache_conditions = False
+    model.clear_condition_cache()
+
+    # end to end: host (pinned) inputs -> H2D -> forward -> D2H of the velocity
+    out_host = torch.empty(step().shape, dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        d = to_dev(host, device)
+        out_host.copy_(model(**d), non_blocking=True)
+
+    e2e_step()
+    ms_e2e = timed_steps(e2e_step, args.steps, dist_on) / args.steps
+    h2d, d2h = nbytes(host), out_host.numel() * 4
+
+    kernels = None
+    if do_profile and rank == 0:
+        ops.profile_start()
+        step()
+        kernels = ops.profile_stop()
+    elif do_profile:
+        step()                                       # keep the collectives of the profiled step matched
+    torch.cuda.synchronize()
+    del model
+    torch.cuda.empty_cache()
+    return dict(ms_step=ms_step, ms_cached=ms_cached, ms_e2e=ms_e2e, h2d=h2d, d2h=d2h, launches=launches,
+                clocks=clocks, kernels=kernels, wl=wl)
+
+
+def kernel_table(kernels, pk):
+    tot = sum(k["ms"] for k in kernels.values()) or 1.0
+    rows = {}
+    for name, k in sorted(kernels.items(), key=lambda kv: -kv[1]["ms"]):
+        tensor = k["flops"] > 0 and ("gemm" in name or "attention_s" in name)
+        s = k["ms"] * 1e-3
+        if tensor:
+            ach, peak, unit = k["flops"] / s / 1e12, pk["tf_sustained"], "TFLOP/s"
+        else:
+            ach, peak, unit = k["bytes"] / s / 1e9, pk["hbm"], "GB/s"
+        rows[name] = dict(calls=k["calls"], ms=round(k["ms"], 3), share=round(k["ms"] / tot, 4),
+                          bound="tensor" if tensor else "hbm", achieved=round(ach, 1), peak=peak, unit=unit,
+                          frac=round(ach / peak, 4))
+    return rows
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="xl_17f_848x1600")
+    ap.add_argument("--no-secondary", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+
+    assert torch.cuda.is_available(), "bench.py (impl ours) needs a CUDA device: there is no CPU fallback"
+    if args.warmup < 3:
+        args.warmup = 3
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+    pk = peaks()
+
+    from magicdrive_v2_b200 import synth
+    res = measure(args.workload, args, rank, world, device, pk)
+    wl = res["wl"]
+    T = synth.latent_frames(wl["t_pix"])
+    cfg = workload_config(args.workload, world)
+    L = 2 + (wl["n_text"] + 1) + wl["n_box"]
+    fl = algorithmic_flops(wl["b"], wl["NC"], T, cfg["tokens_per_frame"], L)
+
+    secondary = None
+    if world == 1 and not args.no_secondary and args.workload != "xl_17f_224x400":
+        r2 = measure("xl_17f_224x400", args, rank, world, device, pk, do_profile=False)
+        c2 = workload_config("xl_17f_224x400", 1)
+        f2 = algorithmic_flops(2, 6, 5, c2["tokens_per_frame"], L)
+        secondary = dict(config=c2, value=1e3 / r2["ms_step"], unit=UNIT, ms_per_step=r2["ms_step"],
+                         value_conditions_cached=1e3 / r2["ms_cached"],
+                         e2e=dict(value=1e3 / r2["ms_e2e"], unit=UNIT, h2d_bytes_per_step=r2["h2d"],
+                                  d2h_bytes_per_step=r2["d2h"]),
+                         gpu_launches=r2["launches"], algorithmic_tflop_per_step=f2["total"] / 1e12,
+                         step_tflops=f2["total"] / (r2["ms_step"] * 1e-3) / 1e12)
+
+    if rank != 0:
+        if world > 1:
+            torch.distributed.destroy_process_group()
+        return
+
+    ktab = kernel_table(res["kernels"], pk)
+    dom = next(iter(ktab))
+    drow = ktab[dom]
+    roofline = dict(kernel=dom, bound=drow["bound"], achieved=drow["achieved"], peak=drow["peak"],
+                    unit=drow["unit"], frac=drow["frac"], traffic=None, share_of_step=drow["share"],
+                    peak_source=pk["source"] + (", sustained bf16 (kernel timed inside a long step)"
+                                                if drow["bound"] == "tensor" else ", copy bandwidth"),
+                    how="CUDA-event pair around every libmdv2 call of one instrumented step, summed per kernel")
+    step_tf = fl["total"] / world / (res["ms_step"] * 1e-3) / 1e12
+    line = dict(metric=METRIC, value=1e3 / res["ms_step"], unit=UNIT, n_gpus=world, steps=args.steps,
+                warmup=args.warmup, ms_per_step=res["ms_step"], higher_is_better=True, scaling="strong",
+                vs_baseline=None, dtype="bf16", data="synthetic", config=cfg,
+                e2e=dict(value=1e3 / res["ms_e2e"], unit=UNIT, h2d_bytes_per_step=res["h2d"],
+                         d2h_bytes_per_step=res["d2h"]),
+                gpu_launches=res["launches"], clocks=res["clocks"], roofline=roofline, kernels=ktab,
+                value_conditions_cached=1e3 / res["ms_cached"],
+                algorithmic_tflop_per_step=fl["total"] / 1e12,
+                step_tflops_per_gpu=step_tf, step_frac_of_bf16_sustained=step_tf / pk["tf_sustained"],
+                step_frac_of_bf16_burst=step_tf / pk["tf_burst"])
+    if secondary:
+        line["secondary"] = secondary
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        sample = CpuSample(args.workload)
+        est, wall = sample.step()
+        line["cpu_baseline"] = dict(value=1.0 / est, unit=UNIT, cores=cores, kind="port", sample=sample.desc,
+                                    sample_wall_s=wall)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -32,6 +32,7 @@ extern "C" {
 
 int mdv2_version(void);
 const char* mdv2_last_error(void);   /* host pointer, thread-local */
+const char* mdv2_last_kernel(void);  /* kernel family launched by the last successful call on this thread */
 
 /* LayerNorm(eps, no affine) -> x·(1+scale)+shift with per-(bi,t) rows of `mod`.
  * Replaces nn.LayerNorm/apex FusedLayerNorm + t2i_modulate + t_mask_select:

@@ -1,15 +1,27 @@
 // attn_sm100.cu — flash attention on tcgen05 / TMEM / TMA (bf16 in, fp32 softmax, bf16 out).
 //
-// One CTA = one (sequence, head, 128-query tile).  warp 0: TMA producer (Q once, K/V ring),
-// warp 1: tcgen05.mma issuer, warps 2-5: softmax (thread = query row = TMEM lane).
-//   S = Q·K^T   : A = Q (K-major, SW128), B = K tile (K-major, SW128)      -> TMEM S[2] (double buffer)
-//   O_j = P·V   : A = P (bf16, written to smem in the SW128 K-major layout), B = V tile (MN-major, SW128)
-// Online softmax state (m, l) and the running output live in the softmax threads' registers; the
-// per-tile PV product is read back from TMEM and folded in with the rescale factor.
-// head_dim 72 is handled without padding in HBM: the TMA box is 64 wide, the second box (d = 64..127)
-// is zero-filled beyond 72 by the TMA unit; QK^T runs K = 80, PV runs N = 80.
-// Several K/V "sets" (cross-view neighbours) are processed back to back and their normalised
-// outputs summed.
+// One CTA = one (sequence, head) x TWO 128-query tiles (256 query rows), 10 warps:
+//   warp 0      TMA producer: Q (both tiles, once), K ring, V ring (independent rings: K_j is released as
+//               soon as both S_t(j) are done, V_j after both PV_t(j))
+//   warp 1      tcgen05.mma issuer (one lane) + TMEM owner
+//   warps 2-5   softmax of query tile 0   (thread = query row = TMEM lane)
+//   warps 6-9   softmax of query tile 1
+// Per K/V tile j and query tile t:
+//   S_t = Q_t · K_j^T   A = Q_t (smem, K-major SW128), B = K_j (smem, K-major SW128)   -> TMEM S_t (fp32)
+//   softmax thread: one tcgen05.ld of its whole S row, running max with LAZY rescaling (the reference
+//     maximum only moves when the row max grows by > 2^8, so O is rescaled in TMEM a handful of times
+//     per row instead of once per tile), p = 2^(s·c − m·c), row sum, bf16 pack, tcgen05.st of P over
+//     the S columns it just consumed
+//   O_t += P_t · V_j    A = P_t (TMEM, bf16 pairs), B = V_j (smem, MN-major SW128)      -> TMEM O_t (fp32)
+// The two query tiles ping-pong: while the tensor core runs PV_0(j) and S_0(j+1), warps 6-9 run the
+// softmax of tile 1, and vice versa.  The tensor pipe executes MMAs in issue order, which is what makes
+// P aliasing S safe: S_t(j+1) is issued after PV_t(j).
+// head_dim 72 is not padded in HBM: TMA boxes are 64 columns wide, the second box (d = 64..127) is
+// zero-filled beyond 72 by the TMA unit; QK^T runs K = 80, PV runs N = 80.
+// Several K/V "sets" (cross-view neighbours) are processed back to back; each set has its own softmax
+// and the bf16 outputs are summed like the reference's gather+sum (stdit3.py:311-322).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 
@@ -19,20 +31,19 @@ int mdv2_make_tmap_3d_heads(CUtensorMap* out, const void* ptr, uint64_t rows, ui
                             uint32_t box_rows);
 
 namespace {
-constexpr int BMQ = 128;        // query rows per CTA
-constexpr int NTHREADS = 192;
-constexpr int CHUNK_COLS = 64;  // bf16 columns per 128-byte swizzle row
+constexpr int BMQ = 128;          // query rows per tile
+constexpr int NTHREADS = 320;
+constexpr int KV_STAGES = 2;
+constexpr int TMEM_COLS = 512;
+constexpr int O_COL0 = 256;       // O_t at columns 256 + 128·t ; S_t (and P_t over it) at 128·t
+constexpr float RESCALE_LOG2 = 8.f;
 
 template <int DP, int BNK>
 struct ACfg {
-  static constexpr int NCH = DP > 64 ? 2 : 1;                 // 64-wide d-chunks per tile
-  static constexpr int Q_BYTES = NCH * BMQ * 128;
-  static constexpr int KV_BYTES = NCH * BNK * 128;            // one of K or V
-  static constexpr int STAGES = 2;
-  static constexpr int P_BYTES = (BNK / 64) * BMQ * 128;
-  static constexpr int SMEM = Q_BYTES + STAGES * 2 * KV_BYTES + P_BYTES + 256 + 1024;
-  static constexpr int S_COLS = BNK;                          // fp32 columns per S buffer
-  static constexpr int O_COL = 2 * 128;                       // TMEM column of the PV tile
+  static constexpr int NCH = DP > 64 ? 2 : 1;                 // 64-wide d-chunks per row
+  static constexpr int Q_BYTES = NCH * BMQ * 128;             // one query tile
+  static constexpr int KV_BYTES = NCH * BNK * 128;            // one K (or V) tile
+  static constexpr int SMEM = 2 * Q_BYTES + KV_STAGES * 2 * KV_BYTES + 256 + 1024;
 };
 
 struct AParams {
@@ -43,6 +54,12 @@ struct AParams {
   const int32_t* kv_map;
 };
 
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 template <int DP, int BNK>
 __global__ void __launch_bounds__(NTHREADS, 1)
 attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
@@ -50,46 +67,46 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
   using C = ACfg<DP, BNK>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sQ = smem;
-  uint8_t* sKV = sQ + C::Q_BYTES;                 // stage s: K at sKV + s*2*KV_BYTES, V right after
-  uint8_t* sP = sKV + C::STAGES * 2 * C::KV_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + C::P_BYTES);
-  uint64_t* q_full = bars;                        // 1
-  uint64_t* k_full = bars + 1;                    // STAGES
-  uint64_t* v_full = k_full + C::STAGES;          // STAGES
-  uint64_t* kv_empty = v_full + C::STAGES;        // STAGES
-  uint64_t* s_full = kv_empty + C::STAGES;        // 2
-  uint64_t* s_empty = s_full + 2;                 // 2
-  uint64_t* p_full = s_empty + 2;                 // 1
-  uint64_t* o_full = p_full + 1;                  // 1
-  uint64_t* o_empty = o_full + 1;                 // 1
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 1);
+  uint8_t* sQ = smem;                                   // tile t at sQ + t·Q_BYTES
+  uint8_t* sK = sQ + 2 * C::Q_BYTES;                    // stage s at sK + s·KV_BYTES
+  uint8_t* sV = sK + KV_STAGES * C::KV_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KV_STAGES * C::KV_BYTES);
+  uint64_t* q_full = bars;                              // 1
+  uint64_t* k_full = bars + 1;                          // KV_STAGES
+  uint64_t* k_empty = k_full + KV_STAGES;
+  uint64_t* v_full = k_empty + KV_STAGES;
+  uint64_t* v_empty = v_full + KV_STAGES;
+  uint64_t* s_full = v_empty + KV_STAGES;               // 2 (per query tile)
+  uint64_t* p_full = s_full + 2;                        // 2
+  uint64_t* o_full = p_full + 2;                        // 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qt = blockIdx.x, h = blockIdx.y, seq = blockIdx.z;
+  const int qp = blockIdx.x, h = blockIdx.y, seq = blockIdx.z;
   const int n_kt = (p.Lk + BNK - 1) / BNK;
   const int n_tiles = n_kt * p.n_sets;
+  const int q_row0 = qp * 2 * BMQ;                      // first query row of this CTA within the sequence
+  const int n_qt = (q_row0 + BMQ < p.Lq) ? 2 : 1;       // the second tile may lie entirely past Lq
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tq);
     prefetch_tmap(&tk);
     prefetch_tmap(&tv);
     mbar_init(q_full, 1);
-    for (int i = 0; i < C::STAGES; ++i) {
+    for (int i = 0; i < KV_STAGES; ++i) {
       mbar_init(&k_full[i], 1);
+      mbar_init(&k_empty[i], 1);
       mbar_init(&v_full[i], 1);
-      mbar_init(&kv_empty[i], 1);
+      mbar_init(&v_empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&s_full[i], 1);
-      mbar_init(&s_empty[i], 4);
+      mbar_init(&p_full[i], 4);
+      mbar_init(&o_full[i], 1);
     }
-    mbar_init(p_full, 4);
-    mbar_init(o_full, 1);
-    mbar_init(o_empty, 4);
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -98,26 +115,29 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
   if (warp == 0) {
     // ================= TMA producer =================
     if (lane == 0) {
-      mbar_expect_tx(q_full, C::Q_BYTES);
-      const int q_row = seq * p.Lq + qt * BMQ;
+      mbar_expect_tx(q_full, n_qt * C::Q_BYTES);
+      for (int t = 0; t < n_qt; ++t) {
+        const int row = seq * p.Lq + q_row0 + t * BMQ;
 #pragma unroll
-      for (int c = 0; c < C::NCH; ++c) tma_load_3d(sQ + c * BMQ * 128, &tq, q_full, c * 64, h, q_row);
-      int stage = 0;
-      uint32_t phase = 0;
+        for (int c = 0; c < C::NCH; ++c) tma_load_3d(sQ + t * C::Q_BYTES + c * BMQ * 128, &tq, q_full, c * 64, h, row);
+      }
+      int j = 0;
       for (int set = 0; set < p.n_sets; ++set) {
         const int kseq = p.kv_map ? p.kv_map[seq * p.n_sets + set] : seq;
-        for (int kt = 0; kt < n_kt; ++kt) {
-          mbar_wait(&kv_empty[stage], phase ^ 1);
-          uint8_t* sk = sKV + stage * 2 * C::KV_BYTES;
-          uint8_t* sv = sk + C::KV_BYTES;
+        for (int kt = 0; kt < n_kt; ++kt, ++j) {
+          const int st = j % KV_STAGES;
+          const uint32_t ph = (uint32_t)((j / KV_STAGES) & 1);
           const int row = kseq * p.Lk + kt * BNK;
-          mbar_expect_tx(&k_full[stage], C::KV_BYTES);
+          mbar_wait(&k_empty[st], ph ^ 1);
+          mbar_expect_tx(&k_full[st], C::KV_BYTES);
 #pragma unroll
-          for (int c = 0; c < C::NCH; ++c) tma_load_3d(sk + c * BNK * 128, &tk, &k_full[stage], c * 64, h, row);
-          mbar_expect_tx(&v_full[stage], C::KV_BYTES);
+          for (int c = 0; c < C::NCH; ++c)
+            tma_load_3d(sK + st * C::KV_BYTES + c * BNK * 128, &tk, &k_full[st], c * 64, h, row);
+          mbar_wait(&v_empty[st], ph ^ 1);
+          mbar_expect_tx(&v_full[st], C::KV_BYTES);
 #pragma unroll
-          for (int c = 0; c < C::NCH; ++c) tma_load_3d(sv + c * BNK * 128, &tv, &v_full[stage], c * 64, h, row);
-          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+          for (int c = 0; c < C::NCH; ++c)
+            tma_load_3d(sV + st * C::KV_BYTES + c * BNK * 128, &tv, &v_full[st], c * 64, h, row);
         }
       }
     }
@@ -125,162 +145,161 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     // ================= MMA issuer =================
     if (lane == 0) {
       constexpr uint32_t idesc_qk = make_idesc_bf16(BMQ, BNK, 0, 0);
-      constexpr uint32_t idesc_pv = make_idesc_bf16(BMQ, DP, 0, 1);     // B (= V) is MN-major
-      constexpr int KSTEPS_QK = DP / 16;
-      auto issue_qk = [&](int j) {
-        const int st = j % C::STAGES, buf = j & 1;
-        mbar_wait(&k_full[st], (uint32_t)((j / C::STAGES) & 1));
-        mbar_wait(&s_empty[buf], (uint32_t)(((j >> 1) & 1) ^ 1));
-        tc_fence_after();
-        const uint32_t aq = smem_u32(sQ), bk = smem_u32(sKV + st * 2 * C::KV_BYTES);
+      constexpr uint32_t idesc_pv = make_idesc_bf16(BMQ, DP, 0, 1);     // A = P from TMEM, B = V is MN-major
+      auto issue_qk = [&](int t, int st) {
+        const uint32_t aq = smem_u32(sQ + t * C::Q_BYTES), bk = smem_u32(sK + st * C::KV_BYTES);
 #pragma unroll
-        for (int ks = 0; ks < KSTEPS_QK; ++ks) {
+        for (int ks = 0; ks < DP / 16; ++ks) {
           const int c = ks / 4, kk = ks % 4;
           const uint64_t da = make_desc_k_sw128(aq + c * BMQ * 128 + kk * 32);
           const uint64_t db = make_desc_k_sw128(bk + c * BNK * 128 + kk * 32);
-          umma_bf16_ss(tmem_base + buf * 128, da, db, idesc_qk, ks != 0);
+          umma_bf16_ss(tmem_base + t * 128, da, db, idesc_qk, ks != 0);
         }
-        umma_commit(&s_full[buf]);
+        umma_commit(&s_full[t]);
       };
       mbar_wait(q_full, 0);
-      issue_qk(0);
+      mbar_wait(&k_full[0], 0);
+      tc_fence_after();
+      for (int t = 0; t < n_qt; ++t) issue_qk(t, 0);
+      umma_commit(&k_empty[0]);
       for (int j = 0; j < n_tiles; ++j) {
-        if (j + 1 < n_tiles) issue_qk(j + 1);
-        const int st = j % C::STAGES;
-        mbar_wait(&v_full[st], (uint32_t)((j / C::STAGES) & 1));
-        mbar_wait(p_full, (uint32_t)(j & 1));
-        mbar_wait(o_empty, (uint32_t)((j & 1) ^ 1));
-        tc_fence_after();
-        const uint32_t ap = smem_u32(sP), bv = smem_u32(sKV + st * 2 * C::KV_BYTES + C::KV_BYTES);
+        const int st = j % KV_STAGES, st1 = (j + 1) % KV_STAGES;
+        const bool more = j + 1 < n_tiles;
+        const bool fresh = (j % n_kt) == 0;              // first tile of a K/V set: O starts over
+        mbar_wait(&v_full[st], (uint32_t)((j / KV_STAGES) & 1));
+        if (more) mbar_wait(&k_full[st1], (uint32_t)(((j + 1) / KV_STAGES) & 1));
+        const uint32_t bv = smem_u32(sV + st * C::KV_BYTES);
+        for (int t = 0; t < n_qt; ++t) {
+          mbar_wait(&p_full[t], (uint32_t)(j & 1));
+          tc_fence_after();
 #pragma unroll
-        for (int ks = 0; ks < BNK / 16; ++ks) {
-          const uint64_t da = make_desc_k_sw128(ap + (ks / 4) * BMQ * 128 + (ks % 4) * 32);
-          const uint64_t db = make_desc_mn_sw128(bv + ks * 16 * 128, BNK * 128, 1024);
-          umma_bf16_ss(tmem_base + C::O_COL, da, db, idesc_pv, ks != 0);
+          for (int ks = 0; ks < BNK / 16; ++ks) {
+            const uint64_t db = make_desc_mn_sw128(bv + ks * 16 * 128, BNK * 128, 1024);
+            umma_bf16_ts(tmem_base + O_COL0 + t * 128, tmem_base + t * 128 + ks * 8, db, idesc_pv,
+                         (ks != 0) || !fresh);
+          }
+          umma_commit(&o_full[t]);
+          if (more) issue_qk(t, st1);
         }
-        umma_commit(o_full);
-        umma_commit(&kv_empty[st]);
+        umma_commit(&v_empty[st]);
+        if (more) umma_commit(&k_empty[st1]);
       }
     }
-  } else {
+  } else if (((warp - 2) >> 2) < n_qt) {
     // ================= softmax warps: thread = query row =================
-    const int quarter = warp & 3;
-    const int row = quarter * 32 + lane;               // row within the q tile == TMEM lane
+    const int t = (warp - 2) >> 2;
+    const int quarter = warp & 3;                      // TMEM lane quarter this warp may touch
+    const int row = quarter * 32 + lane;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    const int q_idx = qt * BMQ + row;
-    float acc_out[DP];
-#pragma unroll
-    for (int d = 0; d < DP; ++d) acc_out[d] = 0.f;
+    const uint32_t s_addr = lane_addr + t * 128, o_addr = lane_addr + O_COL0 + t * 128;
+    const int q_idx = q_row0 + t * BMQ + row;
+    const float c = p.scale_log2;
+    bf16* orow = p.out + ((int64_t)seq * p.Lq + q_idx) * p.ldo + (int64_t)h * p.D;
     int j = 0;
-    bool pv_pending = false;                           // a PV tile is in flight / waiting to be folded
     for (int set = 0; set < p.n_sets; ++set) {
-      float o_run[DP];
-#pragma unroll
-      for (int d = 0; d < DP; ++d) o_run[d] = 0.f;
-      float m_run = -INFINITY, l_run = 0.f;
+      float m_used = -INFINITY, l_run = 0.f;
       for (int kt = 0; kt < n_kt; ++kt, ++j) {
-        const int buf = j & 1;
-        const int kv_left = p.Lk - kt * BNK;           // valid keys in this tile (may exceed BNK)
-        mbar_wait(&s_full[buf], (uint32_t)((j >> 1) & 1));
+        mbar_wait(&s_full[t], (uint32_t)(j & 1));
         tc_fence_after();
-        // pass 1: row max
-        float tmax = -INFINITY;
+        uint32_t sr[BNK];
 #pragma unroll
-        for (int c0 = 0; c0 < BNK; c0 += 32) {
-          uint32_t r[32];
-          tmem_ld_x32(lane_addr + buf * 128 + c0, r);
-          tmem_ld_wait();
+        for (int c0 = 0; c0 < BNK; c0 += 32) tmem_ld_x32(s_addr + c0, sr + c0);
+        tmem_ld_wait();
+        if (kt == n_kt - 1) {                          // ragged last tile: keys past Lk do not exist
+          const int kv_left = p.Lk - kt * BNK;
+          if (kv_left < BNK) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (c0 + i < kv_left) tmax = fmaxf(tmax, __uint_as_float(r[i]));
-        }
-        const float m_new = fmaxf(m_run, tmax);
-        const float alpha = exp2f((m_run - m_new) * p.scale_log2);   // 0 on the first tile (m_run = -inf)
-        const float moff = m_new * p.scale_log2;
-        // the previous PV must have finished reading P before it is overwritten
-        if (pv_pending) {
-          mbar_wait(o_full, (uint32_t)((j - 1) & 1));
-          tc_fence_after();
-          // fold the previous PV tile into the running output (rescale was applied when it was formed)
-          uint32_t r[32];
-#pragma unroll
-          for (int c0 = 0; c0 < DP; c0 += 16) {
-            tmem_ld_x16(lane_addr + C::O_COL + c0, r);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 16; ++i) o_run[c0 + i] += __uint_as_float(r[i]);
-          }
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(o_empty);
-          pv_pending = false;
-        }
-#pragma unroll
-        for (int d = 0; d < DP; ++d) o_run[d] *= alpha;
-        l_run *= alpha;
-        // pass 2: probabilities -> bf16 -> smem (SW128 K-major), row sum
-        float lsum = 0.f;
-#pragma unroll
-        for (int c0 = 0; c0 < BNK; c0 += 32) {
-          uint32_t r[32];
-          tmem_ld_x32(lane_addr + buf * 128 + c0, r);
-          tmem_ld_wait();
-          float pr[32];
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const float e = exp2f(__uint_as_float(r[i]) * p.scale_log2 - moff);
-            pr[i] = (c0 + i < kv_left) ? e : 0.f;
-            lsum += pr[i];
-          }
-          uint8_t* prow = sP + (c0 / 64) * BMQ * 128 + row * 128;
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            Vec16<bf16> pk;
-            pk.pack(pr + u * 8);
-            const int unit = ((c0 % 64) / 8 + u) ^ (row & 7);
-            *reinterpret_cast<uint4*>(prow + unit * 16) = pk.raw;
+            for (int i = 0; i < BNK; ++i)
+              if (i >= kv_left) sr[i] = 0xff800000u;   // -inf
           }
         }
-        l_run += lsum;
-        m_run = m_new;
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < BNK; i += 4) {
+          mx0 = fmaxf(mx0, __uint_as_float(sr[i]));
+          mx1 = fmaxf(mx1, __uint_as_float(sr[i + 1]));
+          mx2 = fmaxf(mx2, __uint_as_float(sr[i + 2]));
+          mx3 = fmaxf(mx3, __uint_as_float(sr[i + 3]));
+        }
+        const float m_new = fmaxf(m_used, fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)));
+        const bool grow = (m_new - m_used) * c > RESCALE_LOG2;          // true on the first tile (m_used = -inf)
+        if (__any_sync(0xffffffffu, grow)) {
+          const float alpha = grow ? ex2((m_used - m_new) * c) : 1.f;  // 0 on the first tile
+          if (grow) m_used = m_new;
+          l_run *= alpha;
+          if (kt > 0) {
+            // rescale the running output in TMEM: PV(j-1) must have completed; PV(j) is not issued
+            // before this warp arrives on p_full below
+            mbar_wait(&o_full[t], (uint32_t)((j - 1) & 1));
+            tc_fence_after();
+#pragma unroll
+            for (int c0 = 0; c0 < DP; c0 += 16) {
+              uint32_t r[16];
+              tmem_ld_x16(o_addr + c0, r);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+              tmem_st_x16(o_addr + c0, r);
+            }
+          }
+        }
+        const float moff = m_used * c;
+        float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+        uint32_t pk[BNK / 2];
+#pragma unroll
+        for (int i = 0; i < BNK; i += 4) {
+          const float e0 = ex2(fmaf(__uint_as_float(sr[i]), c, -moff));
+          const float e1 = ex2(fmaf(__uint_as_float(sr[i + 1]), c, -moff));
+          const float e2 = ex2(fmaf(__uint_as_float(sr[i + 2]), c, -moff));
+          const float e3 = ex2(fmaf(__uint_as_float(sr[i + 3]), c, -moff));
+          l0 += e0; l1 += e1; l2 += e2; l3 += e3;
+          __nv_bfloat162 b01 = __floats2bfloat162_rn(e0, e1), b23 = __floats2bfloat162_rn(e2, e3);
+          pk[i / 2] = *reinterpret_cast<uint32_t*>(&b01);
+          pk[i / 2 + 1] = *reinterpret_cast<uint32_t*>(&b23);
+        }
+        l_run += (l0 + l1) + (l2 + l3);
+#pragma unroll
+        for (int c0 = 0; c0 < BNK / 2; c0 += 32) tmem_st_x32(s_addr + c0, pk + c0);
+        tmem_st_wait();
         tc_fence_before();
-        fence_async_smem();
         __syncwarp();
-        if (lane == 0) {
-          mbar_arrive(&s_empty[buf]);
-          mbar_arrive(p_full);
-        }
-        pv_pending = true;
-        // last tile of a set: wait for its PV, finish the set
+        if (lane == 0) mbar_arrive(&p_full[t]);
         if (kt == n_kt - 1) {
-          mbar_wait(o_full, (uint32_t)(j & 1));
+          // end of a K/V set: normalise, round to bf16, add to what earlier sets left in `out`
+          mbar_wait(&o_full[t], (uint32_t)(j & 1));
           tc_fence_after();
-          uint32_t r[32];
-#pragma unroll
-          for (int c0 = 0; c0 < DP; c0 += 16) {
-            tmem_ld_x16(lane_addr + C::O_COL + c0, r);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 16; ++i) o_run[c0 + i] += __uint_as_float(r[i]);
-          }
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(o_empty);
-          pv_pending = false;
           const float inv = 1.f / l_run;
 #pragma unroll
-          for (int d = 0; d < DP; ++d) acc_out[d] += o_run[d] * inv;
-        }
-      }
-    }
-    if (q_idx < p.Lq) {
-      bf16* op = p.out + ((int64_t)seq * p.Lq + q_idx) * p.ldo + (int64_t)h * p.D;
+          for (int c0 = 0; c0 < DP; c0 += 16) {
+            uint32_t r[16];
+            tmem_ld_x16(o_addr + c0, r);
+            tmem_ld_wait();
+            if (q_idx < p.Lq) {
 #pragma unroll
-      for (int d = 0; d < DP; d += 8) {
-        if (d < p.D) {
-          Vec16<bf16> pk;
-          pk.pack(acc_out + d);
-          *reinterpret_cast<uint4*>(op + d) = pk.raw;
+              for (int u = 0; u < 2; ++u) {
+                const int d = c0 + u * 8;
+                if (d < p.D) {
+                  float f[8];
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(r[u * 8 + i]) * inv;
+                  Vec16<bf16> o;
+                  o.pack(f);
+                  if (set > 0) {
+                    Vec16<bf16> prev;
+                    prev.raw = *reinterpret_cast<const uint4*>(orow + d);
+                    float g[8], a[8];
+                    prev.unpack(g);
+                    o.unpack(a);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) a[i] += g[i];
+                    o.pack(a);
+                  }
+                  *reinterpret_cast<uint4*>(orow + d) = o.raw;
+                }
+              }
+            }
+          }
+          tc_fence_before();
         }
       }
     }
@@ -289,12 +308,10 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
-}  // namespace
 
-namespace {
 template <int DP, int BNK>
 int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p, int n_seq,
                 cudaStream_t st) {
@@ -308,7 +325,7 @@ int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap&
     }
     configured = true;
   }
-  dim3 grid((p.Lq + BMQ - 1) / BMQ, p.H, n_seq);
+  dim3 grid((p.Lq + 2 * BMQ - 1) / (2 * BMQ), p.H, n_seq);
   attn_sm100_kernel<DP, BNK><<<grid, NTHREADS, C::SMEM, st>>>(tq, tk, tv, p);
   MDV2_CHECK_LAUNCH("attention_sm100");
   return MDV2_OK;
@@ -330,12 +347,11 @@ int mdv2_attention_sm100(const void* q, int64_t ldq, const void* k, int64_t ldk,
   MDV2_REQUIRE(n_seq <= 65535, "attention_sm100: too many sequences");
   MDV2_REQUIRE(((uintptr_t)q % 16 == 0) && ((uintptr_t)k % 16 == 0) && ((uintptr_t)v % 16 == 0) && ((uintptr_t)out % 16 == 0),
                "attention_sm100: operands must be 16-byte aligned");
-  // number of K/V sequences addressable: kv_map may point anywhere inside [0, n_seq) for self/cross-view;
-  // for cross-attention the K/V tensor has its own n_seq·Lk rows
   const int bnk = Lk <= 64 ? 64 : 128;
   CUtensorMap tq, tk, tv;
   int rc = mdv2_make_tmap_3d_heads(&tq, q, (uint64_t)n_seq * Lq, H, D, ldq, BMQ);
   if (rc) return rc;
+  // K/V hold their own number of sequences (cross-attention) — only the row count bounds the TMA zero fill
   rc = mdv2_make_tmap_3d_heads(&tk, k, (uint64_t)n_seq * Lk, H, D, ldk, bnk);
   if (rc) return rc;
   rc = mdv2_make_tmap_3d_heads(&tv, v, (uint64_t)n_seq * Lk, H, D, ldv, bnk);

@@ -10,6 +10,7 @@
 #define MDV2_VERSION 100
 
 void mdv2_set_error(const char* fmt, ...);
+void mdv2_note_kernel(const char* name);   // name of the kernel family the last C-ABI call launched
 
 #define MDV2_REQUIRE(cond, ...)            \
   do {                                     \
@@ -26,6 +27,7 @@ void mdv2_set_error(const char* fmt, ...);
       mdv2_set_error("%s: launch failed: %s", name, cudaGetErrorString(e_)); \
       return MDV2_ECUDA;                                                     \
     }                                                                        \
+    mdv2_note_kernel(name);                                                  \
   } while (0)
 
 typedef __nv_bfloat16 bf16;

@@ -12,6 +12,9 @@ void mdv2_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 extern "C" const char* mdv2_last_error(void) { return g_err; }
+static thread_local const char* g_kernel = "";
+void mdv2_note_kernel(const char* name) { g_kernel = name; }
+extern "C" const char* mdv2_last_kernel(void) { return g_kernel; }
 extern "C" int mdv2_version(void) { return MDV2_VERSION; }
 
 // ------------------------------------------------------------------------------------------------

@@ -28,6 +28,7 @@ _vp, _i64, _i32, _f32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_
 
 _lib.mdv2_version.restype = _i32
 _lib.mdv2_last_error.restype = ctypes.c_char_p
+_lib.mdv2_last_kernel.restype = ctypes.c_char_p
 _lib.mdv2_ln_modulate.argtypes = [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _i32, _vp]
 _lib.mdv2_gemm.argtypes = [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _f32, _vp, _i32, _i32,
                            _vp, _i64, _i64, _i64, _i32, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _f32, _i32, _i32, _vp]
@@ -41,7 +42,7 @@ for _f in ("mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention", "mdv2_temporal_att
            "mdv2_unpatchify"):
     getattr(_lib, _f).restype = _i32
 
-EXPORTS = ("mdv2_version", "mdv2_last_error", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention",
+EXPORTS = ("mdv2_version", "mdv2_last_error", "mdv2_last_kernel", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention",
            "mdv2_temporal_attention", "mdv2_patchify", "mdv2_unpatchify")
 
 # kernel-launch counter (bench.py reports it as gpu_launches); +1 per C-ABI call that launches
@@ -81,6 +82,48 @@ def _stream():
     return torch.cuda.current_stream().cuda_stream
 
 
+# per-call device timing (bench.py's kernel breakdown): a list of
+# (kernel family, algorithmic flops, algorithmic bytes, start event, end event) while enabled
+_prof = None
+
+
+def profile_start():
+    global _prof
+    _prof = []
+
+
+def profile_stop():
+    """-> {kernel family: dict(calls, ms, flops, bytes)}; synchronises."""
+    global _prof
+    rec, _prof = _prof, None
+    torch.cuda.synchronize()
+    out = {}
+    for kind, fl, by, e0, e1 in rec or []:
+        d = out.setdefault(kind, dict(calls=0, ms=0.0, flops=0.0, bytes=0.0))
+        d["calls"] += 1
+        d["ms"] += e0.elapsed_time(e1)
+        d["flops"] += fl
+        d["bytes"] += by
+    return out
+
+
+def _t0():
+    if _prof is None:
+        return None
+    e = torch.cuda.Event(enable_timing=True)
+    e.record()
+    return e
+
+
+def _t1(e0, tag, flops, nbytes):
+    if e0 is None:
+        return
+    e1 = torch.cuda.Event(enable_timing=True)
+    e1.record()
+    kind = _lib.mdv2_last_kernel().decode()
+    _prof.append((kind + tag, float(flops), float(nbytes), e0, e1))
+
+
 def _check(rc: int, name: str):
     global launches
     if rc != 0:
@@ -93,8 +136,10 @@ def ln_modulate(x, out, mod, k_shift, k_scale, geo, eps=1e-6):
     N, C = x.shape
     assert x.is_contiguous() and out.is_contiguous() and mod.is_contiguous() and mod.dtype == torch.float32
     assert mod.shape[-1] == C and out.shape == x.shape and out.dtype == x.dtype
+    e0 = _t0()
     _check(_lib.mdv2_ln_modulate(_ptr(x), _ptr(out), _ptr(mod), N, C, mod.shape[-2], k_shift, k_scale, T, S, NC,
                                  eps, _dt(x), _stream()), "mdv2_ln_modulate")
+    _t1(e0, "", 0, 2 * N * C * x.element_size())
     return out
 
 
@@ -126,9 +171,11 @@ def gemm(a, w, bias, out, geo=None, act=None, bias_scale=1.0, gate=None, res=Non
         qw_t, kw_t, hd, nq, nk = rms
         qw, kw = _ptr(qw_t, a.dtype), _ptr(kw_t, a.dtype)
     be = default_backend if backend is None else _BACKENDS[backend]
+    e0 = _t0()
     _check(_lib.mdv2_gemm(pa, lda, pw, ldw, _ptr(bias, a.dtype) if bias is not None else None, po, ldo, M, N, K,
                           1 if act == "gelu" else 0, float(bias_scale), gm, modK, kg, pr, ldr, rmod, rdiv, T, S, NC,
                           qw, kw, hd, nq, nk, 1e-6, _dt(a), be, _stream()), "mdv2_gemm")
+    _t1(e0, "", 2.0 * M * N * K, (M * K + N * K + M * N * (2 if res is not None else 1)) * a.element_size())
     return out
 
 
@@ -144,8 +191,12 @@ def attention(q, k, v, out, n_seq, Lq, Lk, H, D, scale, kv_map=None, backend=Non
         assert kv_map.dtype == torch.int32 and kv_map.is_contiguous() and kv_map.shape[0] == n_seq
         n_sets, pm = kv_map.shape[1], _ptr(kv_map)
     be = default_backend if backend is None else _BACKENDS[backend]
+    e0 = _t0()
     _check(_lib.mdv2_attention(pq, ldq, pk, ldk, pv, ldv, po, ldo, n_seq, Lq, Lk, H, D, float(scale), pm, n_sets,
                                _dt(q), be, _stream()), "mdv2_attention")
+    tag = "[cross]" if Lk <= 512 and Lq != Lk else ("[xview]" if n_sets > 1 else "[self]")
+    _t1(e0, tag, 4.0 * n_seq * Lq * Lk * H * D * n_sets,
+        (2 * q.shape[0] + 2 * n_sets * n_seq * Lk) * H * D * q.element_size())
     return out
 
 
@@ -154,8 +205,10 @@ def temporal_attention(qkv, cos, sin, out, B, T, S, H, D, scale):
     po, ldo = _rows2d(out)
     assert qkv.shape == (B * T * S, 3 * H * D) and out.shape == (B * T * S, H * D)
     assert cos.dtype == torch.float32 and cos.is_contiguous() and cos.shape == (T, D) and sin.shape == (T, D)
+    e0 = _t0()
     _check(_lib.mdv2_temporal_attention(pq, ld, _ptr(cos), _ptr(sin), po, ldo, B, T, S, H, D, float(scale),
                                         _dt(qkv), _stream()), "mdv2_temporal_attention")
+    _t1(e0, "", 4.0 * B * S * T * T * H * D, 4 * B * T * S * H * D * qkv.element_size())
     return out
 
 

@@ -360,7 +360,8 @@ class MagicDriveSTDiT3(PreTrainedModel):
         ops.gemm(m0, self.before_proj.weight, self.before_proj.bias, m)
         out = dict(cond=cond, y_kv=y_kv, m=m.view(b, T, S, C), L=L, y_frames=Tc)
         if self.cache_conditions:
-            self._cond_cache = (key, out)
+            # the key holds ids / data pointers: keep the keyed tensors alive so neither can be recycled
+            self._cond_cache = (key, out, flat)
         return out
 
     # ------------------------------------------------------------------------------------------

@@ -168,7 +168,7 @@ _SMALL_INIT = ("mva_proj.", "after_proj.", "before_proj.", "final_proj.")
 
 
 @torch.no_grad()
-def fill_params(model: torch.nn.Module, seed: int = 0):
+def fill_params(model: torch.nn.Module, seed: int = 0, on_device: bool = False):
     """Deterministic, construction-order-independent weights: every state-dict entry is filled from
     a generator seeded by (seed, crc32(name)), so the reference module, the oracle and the native
     drop-in get bit-identical parameters without shipping a checkpoint.  Scales follow the
@@ -178,8 +178,11 @@ def fill_params(model: torch.nn.Module, seed: int = 0):
     for name, t in sorted(model.state_dict().items()):
         if not t.is_floating_point() or name.endswith("rope.freqs") or name.endswith("inv_freq"):
             continue
-        g = torch.Generator().manual_seed((seed * 1000003 + zlib.crc32(name.encode())) % (2 ** 63))
-        r = torch.randn(t.shape, generator=g)
+        sd_ = (seed * 1000003 + zlib.crc32(name.encode())) % (2 ** 63)
+        if on_device:      # bench.py: same recipe with the device RNG (2 B parameters; values differ from CPU)
+            r = torch.randn(t.shape, generator=torch.Generator(device=t.device).manual_seed(sd_), device=t.device)
+        else:
+            r = torch.randn(t.shape, generator=torch.Generator().manual_seed(sd_))
         small = any(k in name for k in _SMALL_INIT) or (
             "blocks_t." in name and (".attn.proj." in name or ".cross_attn.proj." in name))
         if t.dim() >= 2:

@@ -67,8 +67,16 @@ def rope(freqs, t):                                 # rotary-embedding-torch 0.5
 
 def naive_attention(q, k, v, scale):                # blocks.py:257-267 / :496-504 / :727-742
     dtype = q.dtype
-    attn = ((q * scale) @ k.transpose(-2, -1)).to(torch.float32).softmax(dim=-1).to(dtype)
-    return attn @ v
+    # same arithmetic per (batch, head); the batch is walked in slices so the [B,H,Lq,Lk] fp32 score
+    # tensor the reference materialises at once (120 GB at S=5600) stays under ~2 GB on the host
+    per = q.shape[1] * q.shape[2] * k.shape[2] * 4
+    step = max(1, int(2e9 // max(per, 1)))
+    outs = []
+    for i in range(0, q.shape[0], step):
+        qi, ki, vi = q[i:i + step], k[i:i + step], v[i:i + step]
+        attn = ((qi * scale) @ ki.transpose(-2, -1)).to(torch.float32).softmax(dim=-1).to(dtype)
+        outs.append(attn @ vi)
+    return outs[0] if len(outs) == 1 else torch.cat(outs, 0)
 
 
 def mlp(p, x):                                      # timm Mlp: fc1 -> GELU(tanh) -> fc2
@@ -352,9 +360,9 @@ def patch_embed(p, x):                                       # blocks.py:132-155
 # ---------------------------------------------------------------------------------------------
 @torch.no_grad()
 def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, width, mv_order_map=None,
-            mask=None, x_mask=None, max_layers=None, **_):
+            mask=None, x_mask=None, max_layers=None, timers=None, **_):
     """sd: state dict (fp32 tensors); cfg: constructor kwargs (synth.model_kwargs).
-    ``max_layers`` truncates the block stack (bench.py's bounded CPU sample only)."""
+    ``max_layers`` truncates the block stack; ``timers`` collects wall time per block kind (bench.py)."""
     p = P(sd)
     C, NH = cfg["hidden_size"], cfg["num_heads"]
     depth, cdepth = cfg["depth"], cfg["control_depth"]
@@ -430,8 +438,13 @@ def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, wid
     has_ct = p.has("control_blocks_t.0.attn.qkv.weight")
 
     def blk(name, i, h, temporal):
-        return block_forward(p.sub(f"{name}.{i}"), h, cond, t_mlp, x_mask, t0_mlp, T, S, NC, mv_order_map, NH,
-                             temporal, freqs if temporal else None)
+        import time
+        t_ = time.perf_counter()
+        r = block_forward(p.sub(f"{name}.{i}"), h, cond, t_mlp, x_mask, t0_mlp, T, S, NC, mv_order_map, NH,
+                          temporal, freqs if temporal else None)
+        if timers is not None:                               # bench.py: wall seconds per block kind
+            timers[name] = timers.get(name, 0.0) + time.perf_counter() - t_
+        return r
     for i in range(depth):                                   # stdit3.py:1173-1198
         x = blk("base_blocks_s", i, x, False)
         if i < cdepth:

@@ -1,0 +1,5 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 300 python -m pytest tests/test_ops_gpu.py -q -x -k "attention_tcgen05" 2>&1 | tail -30 | tee gpurun_out/ops_attn_tc.log
+timeout 300 python tools/bench_attn.py 2>&1 | tail -20 | tee gpurun_out/bench_attn.log
+timeout 600 python -m pytest tests/test_model_gpu.py -q -s 2>&1 | tail -30 | tee gpurun_out/model.log
