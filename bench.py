@@ -296,9 +296,12 @@ def measure(wl_name, args, rank, world, device, pk, do_profile=True):
 
     kernels = None
     if do_profile and rank == 0:
+        # cudaProfilerStart/Stop bracket exactly this step: `ncu --profile-from-start off` captures one forward
+        torch.cuda.profiler.start()
         ops.profile_start()
         step()
         kernels = ops.profile_stop()
+        torch.cuda.profiler.stop()
     elif do_profile:
         step()                                       # keep the collectives of the profiled step matched
     torch.cuda.synchronize()

@@ -200,10 +200,137 @@ __global__ void __launch_bounds__(128) temporal_attn_kernel(const T* __restrict_
   }
 }
 
+
+// bf16 fast path (T <= 8, D % 8 == 0, D <= 128): a 16-lane group per (β, s, head), each lane owning one
+// 16-byte vector (8 head dims = 4 RoPE pairs) of q/k/v.  Every global access is a 16-byte vector and all
+// 3·T loads of a lane are issued before the first use, so each SM keeps tens of KB in flight.
+template <int TMAX>
+__global__ void __launch_bounds__(256) temporal_attn_vec_kernel(const bf16* __restrict__ qkv, int64_t ld,
+                                                                const float* __restrict__ cos_t,
+                                                                const float* __restrict__ sin_t,
+                                                                bf16* __restrict__ out, int64_t ldo,
+                                                                int64_t n_units, int S, int H, int D,
+                                                                float scale) {
+  constexpr int Tn = TMAX;                               // exact frame count: every t-loop fully unrolls
+  const int l = threadIdx.x & 15;
+  const int64_t unit = (int64_t)blockIdx.x * 16 + (threadIdx.x >> 4);
+  const bool active = unit < n_units && l * 8 < D;
+  const int64_t u = unit < n_units ? unit : n_units - 1;
+  const int h = (int)(u % H);
+  const int64_t bs = u / H;
+  const int s = (int)(bs % S);
+  const int64_t beta = bs / S;
+  const int C = H * D;
+  const int d0 = active ? l * 8 : 0;
+  const bf16* base = qkv + ((beta * Tn) * S + s) * ld + (int64_t)h * D + d0;
+  const int64_t tstride = (int64_t)S * ld;
+  uint4 qraw[TMAX], kraw[TMAX], vraw[TMAX];
+#pragma unroll
+  for (int t = 0; t < TMAX; ++t) {
+    if (t < Tn && active) {
+      const bf16* rp = base + t * tstride;
+      qraw[t] = *reinterpret_cast<const uint4*>(rp);
+      kraw[t] = *reinterpret_cast<const uint4*>(rp + C);
+      vraw[t] = *reinterpret_cast<const uint4*>(rp + 2 * C);
+    } else {
+      qraw[t] = kraw[t] = vraw[t] = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+  auto rope8 = [&](const uint4& raw, int t, float mul, float* o) {
+    Vec16<bf16> vv;
+    vv.raw = raw;
+    float f[8];
+    vv.unpack(f);
+    const float4 c0 = *reinterpret_cast<const float4*>(cos_t + t * D + d0);
+    const float4 c1 = *reinterpret_cast<const float4*>(cos_t + t * D + d0 + 4);
+    const float4 s0 = *reinterpret_cast<const float4*>(sin_t + t * D + d0);
+    const float4 s1 = *reinterpret_cast<const float4*>(sin_t + t * D + d0 + 4);
+    const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+    const float sn[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+    for (int i = 0; i < 8; i += 2) {
+      o[i] = (f[i] * cs[i] - f[i + 1] * sn[i]) * mul;
+      o[i + 1] = (f[i + 1] * cs[i + 1] + f[i] * sn[i + 1]) * mul;
+    }
+  };
+  float kk[TMAX][8], vv[TMAX][8];
+#pragma unroll
+  for (int t = 0; t < TMAX; ++t) {
+    if (t < Tn) {
+      rope8(kraw[t], t, 1.f, kk[t]);
+      Vec16<bf16> tv;
+      tv.raw = vraw[t];
+      tv.unpack(vv[t]);
+    }
+  }
+#pragma unroll
+  for (int tq = 0; tq < TMAX; ++tq) {
+    if (tq < Tn) {
+      float q[8];
+      rope8(qraw[tq], tq, scale, q);
+      float sc[TMAX];
+      float mx = -INFINITY;
+#pragma unroll
+      for (int t = 0; t < TMAX; ++t) {
+        if (t < Tn) {
+          float a = 0.f;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) a += q[i] * kk[t][i];
+#pragma unroll
+          for (int o = 8; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+          sc[t] = a;
+          mx = fmaxf(mx, a);
+        }
+      }
+      float den = 0.f;
+#pragma unroll
+      for (int t = 0; t < TMAX; ++t) {
+        if (t < Tn) {
+          sc[t] = __expf(sc[t] - mx);
+          den += sc[t];
+        }
+      }
+      const float inv = 1.f / den;
+      float o8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int t = 0; t < TMAX; ++t) {
+        if (t < Tn) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) o8[i] += sc[t] * vv[t][i];
+        }
+      }
+      if (active) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o8[i] *= inv;
+        Vec16<bf16> ov;
+        ov.pack(o8);
+        *reinterpret_cast<uint4*>(out + ((beta * Tn + tq) * S + s) * ldo + (int64_t)h * D + d0) = ov.raw;
+      }
+    }
+  }
+}
+
 template <typename T>
 static int launch_temporal(const void* qkv, int64_t ld, const float* c, const float* s, void* out, int64_t ldo,
                            int B, int Tn, int S, int H, int D, float scale, cudaStream_t st) {
   const int64_t n_warps = (int64_t)B * S * H;
+  if constexpr (sizeof(T) == 2) {
+    if (Tn <= 8 && D % 8 == 0 && D <= 128 && ld % 8 == 0 && ldo % 8 == 0 && ((uintptr_t)qkv % 16 == 0) &&
+        ((uintptr_t)out % 16 == 0)) {
+      const unsigned nb = (unsigned)((n_warps + 15) / 16);
+#define TV_CASE(TT)                                                                                              \
+  case TT:                                                                                                       \
+    temporal_attn_vec_kernel<TT><<<nb, 256, 0, st>>>((const bf16*)qkv, ld, c, s, (bf16*)out, ldo, n_warps, S, H, D, \
+                                                     scale);                                                     \
+    break
+      switch (Tn) {
+        TV_CASE(1); TV_CASE(2); TV_CASE(3); TV_CASE(4); TV_CASE(5); TV_CASE(6); TV_CASE(7); TV_CASE(8);
+      }
+#undef TV_CASE
+      MDV2_CHECK_LAUNCH("temporal_attention");
+      return MDV2_OK;
+    }
+  }
   dim3 grid((unsigned)((n_warps + 3) / 4)), block(128);
   const int ppl = (D / 2 + 31) / 32;
 #define TA_CASE(TM, PP)                                                                                \
