@@ -1,10 +1,14 @@
 // gemm_sm100.cu — bf16 GEMM  out = epilogue(A[M,K] · W[N,K]^T)  on the 5th-gen tensor cores.
 //
-// Persistent, warp-specialised: warp 0 = TMA producer (A and W tiles, 128-byte swizzle), warp 1 =
-// tcgen05.mma issuer (one elected lane) + TMEM owner, warps 2-5 = epilogue (TMEM -> registers ->
-// fused bias / per-head RMSNorm / GELU -> shared staging -> gate / residual -> coalesced stores).
-// Two TMEM accumulator stages let the epilogue of tile i overlap the main loop of tile i+1.
-// Tile: 128 x BN x 64, UMMA 128 x BN x 16, fp32 accumulate in TMEM.
+// Persistent, warp-specialised, CTA PAIRS (cluster of 2, tcgen05 cta_group::2): one pair computes a
+// 256 x BN output tile.  Each CTA loads its 128 rows of A and its BN/2 rows of W per 64-wide k-block
+// (TMA, 128-byte swizzle; the bytes of both CTAs are counted on the leader's mbarrier), the leader's
+// warp 1 issues UMMA 256 x BN x 16 for the pair, and each CTA's TMEM receives the fp32 accumulators of
+// its own 128 rows.  Sharing W across the pair halves the shared-memory traffic per SM — the single-CTA
+// 128 x 256 tile measured 68 % tensor-pipe activity, exactly the 128 B/clk smem limit (ncu, profiles/).
+// warp 0 = TMA producer, warp 1 = MMA issuer (leader) + TMEM owner, warps 2-9 = epilogue (TMEM ->
+// registers -> fused bias / per-head RMSNorm / GELU -> shared staging -> gate / residual -> coalesced
+// stores).  Two TMEM accumulator stages let the epilogue of tile i overlap the main loop of tile i+1.
 #include <mutex>
 #include <unordered_map>
 
@@ -14,7 +18,7 @@
 using namespace sm100;
 
 namespace {
-constexpr int BM = 128, BK = 64;
+constexpr int BM = 128, BK = 64;                     // rows per CTA (256 per pair), k-block
 constexpr int A_BYTES = BM * BK * 2;
 constexpr int NUM_EPI_WARPS = 8;                      // 2 per TMEM lane quarter, interleaved over column chunks
 constexpr int NUM_THREADS = 64 + NUM_EPI_WARPS * 32;
@@ -23,7 +27,7 @@ constexpr int TMEM_COLS = 512, ACC_STRIDE = 256;
 template <int BN, int HD>
 struct Cfg {
   static constexpr int CW = HD ? HD : 64;                // epilogue chunk width (columns)
-  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int B_BYTES = (BN / 2) * BK * 2;      // this CTA's half of the W tile
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int PITCH = ((CW * 2 / 16) % 2 == 1) ? CW * 2 : CW * 2 + 16;   // odd multiple of 16 B
   static constexpr int EPW = 32 * PITCH + 512 + 320;       // per warp: staging + row info + bias (fp32)
@@ -49,7 +53,7 @@ struct Params {
 };
 
 template <int BN, int HD>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                   const Params p) {
   using C = Cfg<BN, HD>;
@@ -64,8 +68,10 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();              // 0 = leader (issues the pair's MMAs)
+  const int64_t pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const int n_tiles_n = p.N / BN;
-  const int64_t n_tiles_m = (p.M + BM - 1) / BM;
+  const int64_t n_tiles_m = (p.M + 2 * BM - 1) / (2 * BM);
   const int64_t n_tiles = n_tiles_m * n_tiles_n;
   const int n_kb = p.K / BK;
 
@@ -78,13 +84,13 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], NUM_EPI_WARPS);
+      mbar_init(&tempty[i], 2 * NUM_EPI_WARPS);         // the epilogue warps of BOTH CTAs (leader's copy is used)
     }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == 1) tmem_alloc_pair(tmem_slot, TMEM_COLS);
   tc_fence_before();
-  __syncthreads();
+  cluster_sync();                                        // barriers + TMEM of both CTAs are ready
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -93,27 +99,28 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const int m0 = (int)(tile / n_tiles_n) * BM, n0 = (int)(tile % n_tiles_n) * BN;
+      for (int64_t tile = pair; tile < n_tiles; tile += n_pairs) {
+        const int m0 = (int)(tile / n_tiles_n) * 2 * BM + (int)rank * BM;
+        const int n0 = (int)(tile % n_tiles_n) * BN + (int)rank * (BN / 2);
         for (int kb = 0; kb < n_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::STAGE_BYTES;
-          mbar_expect_tx(&full[stage], C::STAGE_BYTES);
-          tma_load_2d(sa, &tmap_a, &full[stage], kb * BK, m0);
-          tma_load_2d(sa + A_BYTES, &tmap_w, &full[stage], kb * BK, n0);
+          if (rank == 0) mbar_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
+          tma_load_2d_pair(sa, &tmap_a, &full[stage], kb * BK, m0);
+          tma_load_2d_pair(sa + A_BYTES, &tmap_w, &full[stage], kb * BK, n0);
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
+    // ===== MMA issuer (leader CTA only) =====
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BN);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      for (int64_t tile = pair; tile < n_tiles; tile += n_pairs) {
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
@@ -124,11 +131,11 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           const uint64_t da = make_desc_k_sw128(sa), db = make_desc_k_sw128(sa + A_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)
-            umma_bf16_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
-          umma_commit(&empty[stage]);
+            umma_bf16_ss_pair(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+          umma_commit_pair(&empty[stage]);
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull[acc]);
+        umma_commit_pair(&tfull[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -145,8 +152,8 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     int acc = 0;
     uint32_t acc_phase = 0;
     const Epilogue<bf16>& ep = p.ep;
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-      const int64_t m0 = (tile / n_tiles_n) * BM;
+    for (int64_t tile = pair; tile < n_tiles; tile += n_pairs) {
+      const int64_t m0 = (tile / n_tiles_n) * 2 * BM + (int64_t)rank * BM;
       const int n0 = (int)(tile % n_tiles_n) * BN;
       {  // per-row epilogue context, once per tile (64-bit divisions stay out of the inner loops)
         const int64_t gr = m0 + quarter * 32 + lane;
@@ -239,15 +246,15 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[acc]);
+      if (lane == 0) mbar_arrive_leader(&tempty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
   tc_fence_before();
-  __syncthreads();
+  cluster_sync();                                        // the peer's smem / TMEM stay valid until both are done
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    tmem_dealloc_pair(tmem_base, TMEM_COLS);
   }
 }
 
@@ -329,8 +336,9 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tw, const Params& p, cudaSt
     }
     configured = true;
   }
-  const int64_t tiles = ((p.M + BM - 1) / BM) * (p.N / BN);
-  const int grid = (int)(tiles < mdv2_num_sms() ? tiles : mdv2_num_sms());
+  const int64_t tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * (p.N / BN);
+  const int64_t pairs = mdv2_num_sms() / 2;
+  const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
   gemm_sm100_kernel<BN, HD><<<grid, NUM_THREADS, C::SMEM, st>>>(ta, tw, p);
   MDV2_CHECK_LAUNCH("gemm_sm100");
   return MDV2_OK;
@@ -368,7 +376,7 @@ int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void
   CUtensorMap ta, tw;
   int rc = mdv2_make_tmap_2d(&ta, a, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BM, BK);
   if (rc) return rc;
-  rc = mdv2_make_tmap_2d(&tw, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)bn, BK);
+  rc = mdv2_make_tmap_2d(&tw, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)bn / 2, BK);
   if (rc) return rc;
   Params p;
   p.M = M; p.N = N; p.K = K; p.ldo = ldo; p.out = (bf16*)out; p.ep = ep;
