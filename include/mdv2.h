@@ -83,6 +83,11 @@ int mdv2_patchify(const void* x, void* out, int Bx, int Cin, int NCi, int T, int
 int mdv2_unpatchify(const void* y, float* out, int b, int NC, int Cout, int T, int Hp, int Wp, int Tx,
                     int Hx, int Wx, int dtype, void* stream);
 
+/* dst[b][a][:] = src[a][b][:] for a contiguous inner run of inner_bytes (multiple of 16): the pack / unpack
+ * re-orderings around the sequence-parallel all-to-alls.  Replaces the tensor_split + contiguous + cat copies of
+ * magicdrivedit/acceleration/communications.py:11-21 and the head/sequence rearranges of blocks.py:571-638. */
+int mdv2_swap01(const void* src, void* dst, int64_t A, int64_t B, int64_t inner_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -100,11 +100,10 @@ class STDiT3Block(nn.Module):
         # (b) LN -> modulate ; (c) self-attention ; (d) gated residual
         ops.ln_modulate(x, ws.xm, mod, 0, 1, geo)
         ops.gemm(ws.xm, a.qkv.weight, a.qkv.bias, ws.qkv, geo=geo, rms=(qn, kn, D, C, C))
-        q, k, v = ws.qkv[:, :C], ws.qkv[:, C:2 * C], ws.qkv[:, 2 * C:]
         if self.temporal:
             ops.temporal_attention(ws.qkv, ctx.rope_cos, ctx.rope_sin, ws.ao, d.B, T, S, H, D, scale)
         else:
-            ctx.spatial_attention(ops, q, k, v, ws.ao, d, None, scale)
+            ctx.spatial_attention(ops, ws.qkv, ws.ao, d, None, scale)
         ops.gemm(ws.ao, a.proj.weight, a.proj.bias, x, geo=geo, gate=(mod, 2), res=x)
 
         # (e) cross-attention onto the condition tokens: un-normed, un-gated
@@ -124,7 +123,7 @@ class STDiT3Block(nn.Module):
             ops.ln_modulate(x, ws.xm, mod_mva, 0, 1, geo)
             ops.gemm(ws.xm, cv.qkv.weight, None, ws.qkv, geo=geo,
                      rms=(cv.q_norm.weight, cv.k_norm.weight, D, C, C))
-            ctx.spatial_attention(ops, q, k, v, ws.ao, d, ctx.kv_map, scale)
+            ctx.spatial_attention(ops, ws.qkv, ws.ao, d, ctx.kv_map, scale)
             # proj(a0) + proj(a1) = W(a0 + a1) + n_nbr·bias ; then gate ; then mva_proj + residual
             ops.gemm(ws.ao, cv.proj.weight, cv.proj.bias, ws.xm, geo=geo,
                      bias_scale=float(ctx.kv_map.shape[1]), gate=(mod_mva, 2))

@@ -3,7 +3,7 @@
 // One CTA = one (sequence, head) x TWO 128-query tiles (256 query rows), 10 warps:
 //   warp 0      TMA producer: Q (both tiles, once), K ring, V ring (independent rings: K_j is released as
 //               soon as both S_t(j) are done, V_j after both PV_t(j))
-//   warp 1      tcgen05.mma issuer (one lane) + TMEM owner
+//   warp 1      tcgen05.mma issuer (warp-uniform control flow, one elected lane per instruction) + TMEM owner
 //   warps 2-5   softmax of query tile 0   (thread = query row = TMEM lane)
 //   warps 6-9   softmax of query tile 1
 // Per K/V tile j and query tile t:
@@ -143,46 +143,58 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    if (lane == 0) {
+    // The whole warp runs the warp-uniform control flow and one elected lane issues each tcgen05 instruction:
+    // descriptors then live in uniform registers and the MMAs of a tile go out back to back (with a lane-0
+    // branch the compiler wrapped every MMA in an R2UR + ELECT loop, ~50 clk per 40-64 clk MMA).  Every
+    // shared-memory descriptor is base + constant (the 14-bit address field never carries).
+    {
       constexpr uint32_t idesc_qk = make_idesc_bf16(BMQ, BNK, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(BMQ, DP, 0, 1);     // A = P from TMEM, B = V is MN-major
+      const uint64_t dq0 = make_desc_k_sw128(smem_u32(sQ));
+      const uint64_t dk0 = make_desc_k_sw128(smem_u32(sK));
+      const uint64_t dv0 = make_desc_mn_sw128(smem_u32(sV), BNK * 128, 1024);
       auto issue_qk = [&](int t, int st) {
-        const uint32_t aq = smem_u32(sQ + t * C::Q_BYTES), bk = smem_u32(sK + st * C::KV_BYTES);
+        const uint64_t da = dq0 + (uint64_t)(t * (C::Q_BYTES >> 4));
+        const uint64_t db = dk0 + (uint64_t)(st * (C::KV_BYTES >> 4));
 #pragma unroll
         for (int ks = 0; ks < DP / 16; ++ks) {
-          const int c = ks / 4, kk = ks % 4;
-          const uint64_t da = make_desc_k_sw128(aq + c * BMQ * 128 + kk * 32);
-          const uint64_t db = make_desc_k_sw128(bk + c * BNK * 128 + kk * 32);
-          umma_bf16_ss(tmem_base + t * 128, da, db, idesc_qk, ks != 0);
+          const uint64_t oa = (uint64_t)((ks / 4) * ((BMQ * 128) >> 4) + (ks % 4) * 2);
+          const uint64_t ob = (uint64_t)((ks / 4) * ((BNK * 128) >> 4) + (ks % 4) * 2);
+          if (elect_one()) umma_bf16_ss(tmem_base + t * 128, da + oa, db + ob, idesc_qk, ks != 0);
         }
-        umma_commit(&s_full[t]);
+        if (elect_one()) umma_commit(&s_full[t]);
+        __syncwarp();
       };
       mbar_wait(q_full, 0);
       mbar_wait(&k_full[0], 0);
       tc_fence_after();
       for (int t = 0; t < n_qt; ++t) issue_qk(t, 0);
-      umma_commit(&k_empty[0]);
+      if (elect_one()) umma_commit(&k_empty[0]);
+      __syncwarp();
       for (int j = 0; j < n_tiles; ++j) {
         const int st = j % KV_STAGES, st1 = (j + 1) % KV_STAGES;
         const bool more = j + 1 < n_tiles;
         const bool fresh = (j % n_kt) == 0;              // first tile of a K/V set: O starts over
         mbar_wait(&v_full[st], (uint32_t)((j / KV_STAGES) & 1));
         if (more) mbar_wait(&k_full[st1], (uint32_t)(((j + 1) / KV_STAGES) & 1));
-        const uint32_t bv = smem_u32(sV + st * C::KV_BYTES);
+        const uint64_t dv = dv0 + (uint64_t)(st * (C::KV_BYTES >> 4));
         for (int t = 0; t < n_qt; ++t) {
           mbar_wait(&p_full[t], (uint32_t)(j & 1));
           tc_fence_after();
 #pragma unroll
-          for (int ks = 0; ks < BNK / 16; ++ks) {
-            const uint64_t db = make_desc_mn_sw128(bv + ks * 16 * 128, BNK * 128, 1024);
-            umma_bf16_ts(tmem_base + O_COL0 + t * 128, tmem_base + t * 128 + ks * 8, db, idesc_pv,
-                         (ks != 0) || !fresh);
-          }
-          umma_commit(&o_full[t]);
+          for (int ks = 0; ks < BNK / 16; ++ks)
+            if (elect_one())
+              umma_bf16_ts(tmem_base + O_COL0 + t * 128, tmem_base + t * 128 + ks * 8,
+                           dv + (uint64_t)(ks * ((16 * 128) >> 4)), idesc_pv, (ks != 0) || !fresh);
+          if (elect_one()) umma_commit(&o_full[t]);
+          __syncwarp();
           if (more) issue_qk(t, st1);
         }
-        umma_commit(&v_empty[st]);
-        if (more) umma_commit(&k_empty[st1]);
+        if (elect_one()) {
+          umma_commit(&v_empty[st]);
+          if (more) umma_commit(&k_empty[st1]);
+        }
+        __syncwarp();
       }
     }
   } else if (((warp - 2) >> 2) < n_qt) {

@@ -358,3 +358,38 @@ extern "C" int mdv2_temporal_attention(const void* qkv, int64_t ld, const float*
   if (dtype == 1) return launch_temporal<bf16>(qkv, ld, cos_t, sin_t, out, ldo, B, T, S, H, D, scale, st);
   MDV2_REQUIRE(false, "temporal_attention: bad dtype");
 }
+
+// ------------------------------------------------------------------------------------------------
+// swap01: dst[b][a][:] = src[a][b][:] with a contiguous inner run of `inner_bytes` (multiple of 16).
+// The four re-orderings around the sequence-parallel all-to-alls are all of this form:
+//   qkv [n·3][p][HpD]      -> send  [p][n·3][HpD]        (heads scatter)
+//   recv [p][β·T][Sl·3·HpD] -> full [β·T][p][Sl·3·HpD]    (sequence gather)
+//   o    [β·T][p][Sl·HpD]   -> send2 [p][β·T][Sl·HpD]
+//   recv2 [p][n][HpD]       -> ao    [n][p][HpD]          (heads gather)
+// Replaces the tensor_split / cat / contiguous copies of communications.py:11-21.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) swap01_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst,
+                                                     uint32_t A, uint32_t B, uint32_t inner, int64_t total) {
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = idx / inner;                   // destination row = b·A + a
+    const uint32_t v = (uint32_t)(idx - row * inner);
+    const uint32_t b = (uint32_t)(row / A), a = (uint32_t)(row - (int64_t)b * A);
+    dst[idx] = src[((int64_t)a * B + b) * inner + v];
+  }
+}
+
+extern "C" int mdv2_swap01(const void* src, void* dst, int64_t A, int64_t B, int64_t inner_bytes, void* stream) {
+  if (A * B * inner_bytes == 0) return MDV2_OK;
+  MDV2_REQUIRE(A > 0 && B > 0 && inner_bytes > 0 && inner_bytes % 16 == 0, "swap01: inner run must be a multiple of 16 bytes");
+  MDV2_REQUIRE(((uintptr_t)src % 16 == 0) && ((uintptr_t)dst % 16 == 0), "swap01: operands must be 16-byte aligned");
+  MDV2_REQUIRE(A < (1ll << 31) && B < (1ll << 31) && inner_bytes / 16 < (1ll << 31), "swap01: dimension too large");
+  const int64_t inner = inner_bytes / 16, total = A * B * inner;
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = (int64_t)mdv2_num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  swap01_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)src, (uint4*)dst, (uint32_t)A,
+                                                                    (uint32_t)B, (uint32_t)inner, total);
+  MDV2_CHECK_LAUNCH("swap01");
+  return MDV2_OK;
+}

@@ -38,12 +38,13 @@ _lib.mdv2_temporal_attention.argtypes = [_vp, _i64, _vp, _vp, _vp, _i64, _i32, _
                                          _i32, _vp]
 _lib.mdv2_patchify.argtypes = [_vp, _vp] + [_i32] * 11 + [_vp]
 _lib.mdv2_unpatchify.argtypes = [_vp, _vp] + [_i32] * 10 + [_vp]
+_lib.mdv2_swap01.argtypes = [_vp, _vp, _i64, _i64, _i64, _vp]
 for _f in ("mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention", "mdv2_temporal_attention", "mdv2_patchify",
-           "mdv2_unpatchify"):
+           "mdv2_unpatchify", "mdv2_swap01"):
     getattr(_lib, _f).restype = _i32
 
 EXPORTS = ("mdv2_version", "mdv2_last_error", "mdv2_last_kernel", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention",
-           "mdv2_temporal_attention", "mdv2_patchify", "mdv2_unpatchify")
+           "mdv2_temporal_attention", "mdv2_patchify", "mdv2_unpatchify", "mdv2_swap01")
 
 # kernel-launch counter (bench.py reports it as gpu_launches); +1 per C-ABI call that launches
 launches = 0
@@ -230,3 +231,13 @@ def unpatchify(yo, out, NC, T, Hp, Wp):
     _check(_lib.mdv2_unpatchify(_ptr(yo), _ptr(out), b, NC, Co, T, Hp, Wp, Tx, Hx, Wx, _dt(yo), _stream()),
            "mdv2_unpatchify")
     return out
+
+
+def swap01(src, dst, A, B, inner):
+    """dst[b][a][:] = src[a][b][:]; ``inner`` elements per contiguous run (both tensors contiguous, same dtype)."""
+    assert src.is_contiguous() and dst.is_contiguous() and src.dtype == dst.dtype
+    assert src.numel() == dst.numel() == A * B * inner
+    e0 = _t0()
+    _check(_lib.mdv2_swap01(_ptr(src), _ptr(dst), A, B, inner * src.element_size(), _stream()), "mdv2_swap01")
+    _t1(e0, "", 0, 2 * src.numel() * src.element_size())
+    return dst

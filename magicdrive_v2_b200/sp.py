@@ -70,22 +70,66 @@ def gather(x: torch.Tensor, group, dim: int) -> torch.Tensor:
     return torch.cat(parts, dim=dim).contiguous()
 
 
-def ulysses_attention(ops, q, k, v, out, d, kv_map, scale, group, p):
-    """q/k/v: views [N_local, C] of one qkv buffer (row stride 3C); out: [N_local, C]."""
-    BT, Sl, H, D = d.B * d.T, d.S, d.H, d.D
+_BUFS = {}
+
+
+def _buf(tag, shape, like):
+    """Per-(tag, shape) scratch reused across the 69 attention calls of a forward (stream-ordered reuse)."""
+    key = (tag, tuple(shape), like.dtype, like.device)
+    t = _BUFS.get(key)
+    if t is None:
+        if len(_BUFS) > 64:
+            _BUFS.clear()
+        t = _BUFS[key] = torch.empty(shape, dtype=like.dtype, device=like.device)
+    return t
+
+
+def ulysses_attention(ops, qkv, out, d, kv_map, scale, group, p):
+    """Spatial / cross-view attention under sequence parallelism (blocks.py:546-645, without its copies).
+
+    qkv: [N_l, 3C] local tokens (rows (β, t, s_l)), columns q|k|v with heads in rank order; out: [N_l, C].
+    The work is split into the b scheduler-batch halves (each closed under the cross-view neighbour map), and
+    the chunks are software-pipelined: while chunk c runs attention, the NCCL stream moves chunk c+1's q/k/v
+    and chunk c-1's output.  Every re-ordering is one `swap01` launch at HBM speed:
+
+        qkv [n·3][p][HpD]        -> send  [p][n·3][HpD]          heads scatter   (then all-to-all)
+        recv [p][β'·T][Sl·3·HpD] -> full  [β'·T][p·Sl][3][HpD]   sequence gather
+        o    [β'·T][p][Sl·HpD]   -> send2 [p][β'·T][Sl·HpD]      (then all-to-all)
+        recv2 [p][n][HpD]        -> out   [n][p·HpD]             heads gather
+    """
+    Sl, H, D, C = d.S, d.H, d.D, d.C
     Hp = H // p
-    qkv = torch.stack([q, k, v], dim=1)                                   # [N_l, 3, C] (copy)
-    send = qkv.view(BT, Sl, 3, p, Hp * D).permute(3, 0, 1, 2, 4).contiguous()    # [p, BT, Sl, 3, HpD]
-    recv = torch.empty_like(send)
-    dist.all_to_all_single(recv, send, group=group)
-    full = recv.permute(1, 0, 2, 3, 4).reshape(BT * p * Sl, 3, Hp * D)    # rows (i, r, sl) = (i, s)
-    full = full.contiguous()
-    o = torch.empty(BT * p * Sl, Hp * D, dtype=q.dtype, device=q.device)
-    ops.attention(full[:, 0], full[:, 1], full[:, 2], o, BT, p * Sl, p * Sl, Hp, D, scale, kv_map=kv_map)
-    send2 = o.view(BT, p, Sl, Hp * D).permute(1, 0, 2, 3).contiguous()     # [p(dst), BT, Sl, HpD]
-    recv2 = torch.empty_like(send2)
-    dist.all_to_all_single(recv2, send2, group=group)
-    out.view(BT, Sl, p, Hp * D).copy_(recv2.permute(1, 2, 0, 3))           # heads back in rank order
+    HpD = Hp * D
+    n_chunks = d.b if d.b > 1 else 1
+    BTc = d.NC * d.T * (d.b // n_chunks)                 # sequences per chunk
+    Nc = BTc * Sl                                        # local tokens per chunk
+    assert qkv.is_contiguous() and out.is_contiguous() and qkv.shape == (d.N, 3 * C)
+    maps = [None] * n_chunks
+    if kv_map is not None:
+        for c in range(n_chunks):
+            m = kv_map[c * BTc:(c + 1) * BTc] - c * BTc
+            maps[c] = m.contiguous()
+    work1, work2 = [None] * n_chunks, [None] * n_chunks
+    recv, recv2 = [None] * n_chunks, [None] * n_chunks
+    for c in range(n_chunks):
+        send = _buf(("send", c), (p, Nc * 3, HpD), qkv)
+        recv[c] = _buf(("recv", c), (p, Nc * 3, HpD), qkv)
+        ops.swap01(qkv[c * Nc:(c + 1) * Nc], send, Nc * 3, p, HpD)
+        work1[c] = dist.all_to_all_single(recv[c], send, group=group, async_op=True)
+    for c in range(n_chunks):
+        full = _buf(("full", c), (BTc * p * Sl, 3 * HpD), qkv)
+        o = _buf(("o", c), (BTc * p * Sl, HpD), qkv)
+        send2 = _buf(("send2", c), (p, Nc, HpD), qkv)
+        recv2[c] = _buf(("recv2", c), (p, Nc, HpD), qkv)
+        work1[c].wait()
+        ops.swap01(recv[c], full, p, BTc, Sl * 3 * HpD)
+        ops.attention(full[:, :HpD], full[:, HpD:2 * HpD], full[:, 2 * HpD:], o, BTc, p * Sl, p * Sl, Hp, D, scale,
+                      kv_map=maps[c])
+        ops.swap01(o, send2, BTc, p, Sl * HpD)
+        work2[c] = dist.all_to_all_single(recv2[c], send2, group=group, async_op=True)
+    for c in range(n_chunks):
+        work2[c].wait()
+        ops.swap01(recv2[c], out[c * Nc:(c + 1) * Nc], p, Nc, HpD)
 
 
 def gather_tokens(yo, d, p, group):

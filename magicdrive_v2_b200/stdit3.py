@@ -516,15 +516,17 @@ class MagicDriveSTDiT3(PreTrainedModel):
         group = self.sp_group if self.sp_group is not None else sp.get_sequence_parallel_group()
         return group, torch.distributed.get_world_size(group), torch.distributed.get_rank(group)
 
-    def _spatial_attention(self, ops, q, k, v, out, d: Dims, kv_map, scale):
-        """Attention over the S tokens of every (β, t) frame; with kv_map the K/V come from the
-        neighbour views and the per-neighbour results are summed (cross-view, P5)."""
+    def _spatial_attention(self, ops, qkv, out, d: Dims, kv_map, scale):
+        """Attention over the S tokens of every (β, t) frame (qkv: [N, 3C], columns q|k|v); with kv_map
+        the K/V come from the neighbour views and the per-neighbour results are summed (cross-view, P5)."""
         group, p, _ = self._sp()
         if p == 1:
-            ops.attention(q, k, v, out, d.B * d.T, d.S, d.S, d.H, d.D, scale, kv_map=kv_map)
+            C = d.C
+            ops.attention(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], out, d.B * d.T, d.S, d.S, d.H, d.D, scale,
+                          kv_map=kv_map)
             return
         from . import sp
-        sp.ulysses_attention(ops, q, k, v, out, d, kv_map, scale, group, p)
+        sp.ulysses_attention(ops, qkv, out, d, kv_map, scale, group, p)
 
     def _sp_gather_tokens(self, yo, d: Dims, p, group):
         from . import sp

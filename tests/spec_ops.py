@@ -105,3 +105,8 @@ def unpatchify(yo, out, NC, T, Hp, Wp):
     y = y.reshape(b, Co * NC, T, Hp * 2, Wp * 2)
     out.copy_(y[:, :, :Tx, :Hx, :Wx])
     return out
+
+
+def swap01(src, dst, A, B, inner):
+    dst.copy_(src.reshape(A, B, inner).transpose(0, 1).reshape(dst.shape))
+    return dst

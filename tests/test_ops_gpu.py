@@ -226,3 +226,14 @@ def test_attention_tcgen05_cross_view_and_cross(D):
 
 def test_attention_tcgen05_xl_shape():
     assert _attn_case(12, 1400, 1400, 16, 72) < 2e-2
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_swap01_bit_exact(dtype):
+    for A, B, inner in ((7, 3, 144), (3, 60, 8 * 37), (1, 5, 64), (12, 1, 72)):
+        src = rnd(A, B, inner, dtype=dtype, seed=A + B)
+        dst = torch.empty(B, A, inner, dtype=dtype, device=DEV)
+        ref = torch.empty_like(dst)
+        ops().swap01(src, dst, A, B, inner)
+        spec_ops.swap01(src, ref, A, B, inner)
+        assert torch.equal(dst, ref)

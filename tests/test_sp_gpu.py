@@ -1,0 +1,58 @@
+"""Sequence parallelism on real GPUs (NCCL, world_size 2): the drop-in through libmdv2 on two ranks must match the
+reference golden vector within the bf16 / fp32 tolerances.  Skipped on boxes with fewer than 2 GPUs."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world, port, wl_name, xm, ret):
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for p in (root, os.path.join(root, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    from helpers import build_model, load_golden, rel_l2
+    from magicdrive_v2_b200 import sp, synth
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        fix = load_golden(f"{wl_name}_{xm}.pt")
+        sp.set_sequence_parallel_group(dist.group.WORLD)
+        for dtype, key in ((torch.float32, "fp32"), (torch.bfloat16, "bf16")):
+            model, wl, kw = build_model(wl_name, enable_sequence_parallelism=True)
+            model = model.to(dev, dtype)
+            inp = synth.to_device(synth.make_inputs(wl, seed=fix["seed"], x_mask=xm, kw=kw), dev)
+            out = model(**inp)
+            torch.cuda.synchronize()
+            ret[(rank, key)] = rel_l2(out.cpu(), fix["out"])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("wl_name,xm", [("tiny_d72", "first0")])
+def test_sequence_parallel_nccl_world2(wl_name, xm):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    world = 2
+    ret = mp.Manager().dict()
+    mp.spawn(_worker, args=(world, _free_port(), wl_name, xm, ret), nprocs=world, join=True)
+    for r in range(world):
+        assert ret[(r, "fp32")] < 1e-4, ret[(r, "fp32")]
+        assert ret[(r, "bf16")] < 1e-2, ret[(r, "bf16")]

@@ -33,8 +33,9 @@ def bench(n_seq, Lq, Lk, H=16, D=72, kind="self", iters=5):
     print(f"{kind:6s} n_seq={n_seq:3d} Lq={Lq:5d} Lk={Lk:5d} D={D}: {ms:8.3f} ms  {fl / ms / 1e9:7.1f} TF/s (algorithmic, D un-padded)", flush=True)
 
 if __name__ == "__main__":
-    bench(60, 5600, 5600)
-    bench(60, 5600, 5600, kind="xview")
-    bench(60, 5600, 62, kind="cross")
-    bench(60, 400, 400)
-    bench(60, 1600, 1600)
+    bench(60, 5600, 5600, iters=int(os.environ.get("ITERS", "5")))
+    if "--quick" not in sys.argv:
+        bench(60, 5600, 5600, kind="xview")
+        bench(60, 5600, 62, kind="cross")
+        bench(60, 400, 400)
+        bench(60, 1600, 1600)

@@ -29,7 +29,32 @@ def bench(M, N, K, iters=20, **kw):
     ms2 = e0.elapsed_time(e1) / iters
     print(f"M={M:7d} N={N:5d} K={K:5d}  mdv2 {ms:8.3f} ms {tf:7.1f} TF   cublas {ms2:8.3f} ms {2.0*M*N*K/ms2/1e9:7.1f} TF", flush=True)
 
+def sustained(M, N, K, secs=1.5, **kw):
+    """Back-to-back launches for `secs` seconds (power-capped clocks), ours vs cuBLAS."""
+    bf = torch.bfloat16
+    a = torch.randn(M, K, device="cuda", dtype=bf)
+    o = torch.empty(M, N, device="cuda", dtype=bf)
+    w = torch.randn(N, K, device="cuda", dtype=bf) * K ** -0.5
+    b = torch.randn(N, device="cuda", dtype=bf)
+    res = {}
+    for name, fn in (("mdv2", lambda: ops.gemm(a, w, b, o, **kw)), ("cublas", lambda: torch.matmul(a, w.t(), out=o))):
+        fn(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+        n = max(10, int(secs * 1e3 / max(e0.elapsed_time(e1), 1e-3)))
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        res[name] = 2.0 * M * N * K * n / e0.elapsed_time(e1) / 1e9
+    print(f"sustained M={M} N={N} K={K}: mdv2 {res['mdv2']:7.1f} TF  cublas {res['cublas']:7.1f} TF", flush=True)
+
+
 if __name__ == "__main__":
+    if "--sustained" in sys.argv:
+        for (N, K) in ((1152, 1152), (3456, 1152), (4608, 1152), (1152, 4608)):
+            sustained(336000, N, K, backend="tcgen05")
+        sys.exit(0)
     for M in (24000, 336000 // 4):
         for (N, K) in ((1152, 1152), (3456, 1152), (4608, 1152), (1152, 4608), (2304, 1152)):
             bench(M, N, K, backend="tcgen05")
