@@ -32,18 +32,24 @@ int mdv2_make_tmap_3d_heads(CUtensorMap* out, const void* ptr, uint64_t rows, ui
 
 namespace {
 constexpr int BMQ = 128;          // query rows per tile
-constexpr int NTHREADS = 320;
-constexpr int KV_STAGES = 2;
+constexpr int NTHREADS = 352;    // TMA, MMA(tile 0), 8 softmax warps, MMA(tile 1)
 constexpr int TMEM_COLS = 512;
 constexpr int O_COL0 = 256;       // O_t at columns 256 + 128·t ; S_t (and P_t over it) at 128·t
+constexpr int Q_COL0 = 336;       // Q_t (bf16 pairs, DP/2 <= 40 columns) at 336 + 128·t, in the gaps behind O_t
 constexpr float RESCALE_LOG2 = 8.f;
+constexpr int ATTN_PF_DEFAULT = 2;   // polynomial 2^x pairs per 8 pairs (0, 2, 3, 4)
 
 template <int DP, int BNK>
 struct ACfg {
   static constexpr int NCH = DP > 64 ? 2 : 1;                 // 64-wide d-chunks per row
   static constexpr int Q_BYTES = NCH * BMQ * 128;             // one query tile
   static constexpr int KV_BYTES = NCH * BNK * 128;            // one K (or V) tile
-  static constexpr int SMEM = 2 * Q_BYTES + KV_STAGES * 2 * KV_BYTES + 256 + 1024;
+  // Q is copied into TMEM before the first MMA, so with 128-key tiles (Q_BYTES == KV_BYTES) its two shared-memory
+  // tiles are recycled as the third K / V stage; the 64-key flavour (single K/V tile) keeps Q apart.
+  static constexpr bool ALIAS_Q = BNK == 128;
+  static constexpr int KV_STAGES = ALIAS_Q ? 3 : 2;
+  static constexpr int SMEM = KV_STAGES * 2 * KV_BYTES + (ALIAS_Q ? 0 : 2 * Q_BYTES) + 256 + 1024;
+  static_assert(!ALIAS_Q || Q_BYTES == KV_BYTES, "Q tile must fit a K/V stage");
 };
 
 struct AParams {
@@ -52,7 +58,16 @@ struct AParams {
   int Lq, Lk, H, D, n_sets;
   float scale_log2;
   const int32_t* kv_map;
+  long long* trace;        // debug timeline (tools/attn_trace.py) or nullptr
+  int dbg;                 // debug switches (MDV2_ATTN_DBG): bit 0 swaps the TMA / MMA warps
 };
+
+constexpr int TRACE_STEPS = 96, TRACE_EV = 12;
+__device__ __forceinline__ long long clk64() {
+  long long t;
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(t)::"memory");
+  return t;
+}
 
 __device__ __forceinline__ float ex2(float x) {
   float y;
@@ -60,66 +75,103 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
-template <int DP, int BNK>
+// 2^x for a pair on the FMA pipe (no MUFU): x = n + f, n = round(x), f in [-1/2, 1/2]; 2^f by the degree-3 minimax
+// polynomial (max rel. error 7.5e-5 = 2^-13.7, far below the bf16 rounding of P), 2^n added into the exponent field.
+__device__ __forceinline__ float2 ex2_poly2(float2 x) {
+  const float MAGIC = 12582912.f;                        // 1.5 * 2^23: x + MAGIC rounds x to an integer in the mantissa
+  x.x = fmaxf(x.x, -126.f);
+  x.y = fmaxf(x.y, -126.f);
+  const float2 t = fadd2(x, make_float2(MAGIC, MAGIC));
+  const float2 nf = fadd2(t, make_float2(-MAGIC, -MAGIC));
+  const float2 f = ffma2(nf, make_float2(-1.f, -1.f), x);
+  float2 q = ffma2(f, make_float2(0.05517202615737915f, 0.05517202615737915f),
+                   make_float2(0.2426111400127411f, 0.2426111400127411f));
+  q = ffma2(q, f, make_float2(0.693260908126831f, 0.693260908126831f));
+  q = ffma2(q, f, make_float2(0.9999280571937561f, 0.9999280571937561f));
+  float2 r;
+  r.x = __uint_as_float(__float_as_uint(q.x) + (__float_as_uint(t.x) << 23));
+  r.y = __uint_as_float(__float_as_uint(q.y) + (__float_as_uint(t.y) << 23));
+  return r;
+}
+// pair index (0..BNK/2) -> evaluated by the polynomial?  PF of every 8 pairs, spread evenly.
+__host__ __device__ constexpr bool poly_pair(int pair, int PF) { return ((pair % 8) * PF) / 8 != (((pair % 8) + 1) * PF) / 8; }
+
+template <int DP, int BNK, int PF = 0, bool TRACE = false>
 __global__ void __launch_bounds__(NTHREADS, 1)
 attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
                   const __grid_constant__ CUtensorMap tv, const AParams p) {
   using C = ACfg<DP, BNK>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sQ = smem;                                   // tile t at sQ + t·Q_BYTES
-  uint8_t* sK = sQ + 2 * C::Q_BYTES;                    // stage s at sK + s·KV_BYTES
+  constexpr int KV_STAGES = C::KV_STAGES;
+  uint8_t* sK = smem;                                   // stage s at sK + s·KV_BYTES
   uint8_t* sV = sK + KV_STAGES * C::KV_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KV_STAGES * C::KV_BYTES);
+  uint8_t* s_end = sV + KV_STAGES * C::KV_BYTES;
+  // Q tile t: over the last K (t = 0) / V (t = 1) stage when aliased, else behind the rings
+  uint8_t* sQ0 = C::ALIAS_Q ? sK + (KV_STAGES - 1) * C::KV_BYTES : s_end;
+  uint8_t* sQ1 = C::ALIAS_Q ? sV + (KV_STAGES - 1) * C::KV_BYTES : s_end + C::Q_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(C::ALIAS_Q ? s_end : s_end + 2 * C::Q_BYTES);
   uint64_t* q_full = bars;                              // 1
   uint64_t* k_full = bars + 1;                          // KV_STAGES
   uint64_t* k_empty = k_full + KV_STAGES;
   uint64_t* v_full = k_empty + KV_STAGES;
   uint64_t* v_empty = v_full + KV_STAGES;
-  uint64_t* s_full = v_empty + KV_STAGES;               // 2 (per query tile)
-  uint64_t* p_full = s_full + 2;                        // 2
-  uint64_t* o_full = p_full + 2;                        // 2
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
+  uint64_t* s_full = v_empty + KV_STAGES;               // [query tile][key half]
+  uint64_t* p_full = s_full + 4;                        // [query tile][key half]
+  uint64_t* o_full = p_full + 4;                        // [query tile][key half]: P·V of that half-step has completed
+  uint64_t* qt_full = o_full + 4;                       // [query tile]: Q_t copied from shared memory into TMEM
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(qt_full + 2);
+  constexpr int HB = 64;                                // keys per half-step (S columns handed over at a time)
+  constexpr int NH = BNK / HB;                          // half-steps per K/V tile
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int tma_warp = 0, mma_warp = 1;             // warp 1 also owns the TMEM allocation
   const int qp = blockIdx.x, h = blockIdx.y, seq = blockIdx.z;
   const int n_kt = (p.Lk + BNK - 1) / BNK;
   const int n_tiles = n_kt * p.n_sets;
   const int q_row0 = qp * 2 * BMQ;                      // first query row of this CTA within the sequence
   const int n_qt = (q_row0 + BMQ < p.Lq) ? 2 : 1;       // the second tile may lie entirely past Lq
+  // debug timeline of one CTA of a middle wave: trace[warp][step][event] = clock64
+  const bool tracing = TRACE && p.trace != nullptr && qp == 3 && h == 1 && seq == (int)gridDim.z / 2;
+  auto mark = [&](int j, int ev) {
+    if constexpr (TRACE) {
+      if (tracing && lane == 0 && j < TRACE_STEPS) p.trace[(warp * TRACE_STEPS + j) * TRACE_EV + ev] = clk64();
+    }
+  };
 
-  if (warp == 0 && lane == 0) {
+  if (warp == tma_warp && lane == 0) {
     prefetch_tmap(&tq);
     prefetch_tmap(&tk);
     prefetch_tmap(&tv);
     mbar_init(q_full, 1);
     for (int i = 0; i < KV_STAGES; ++i) {
       mbar_init(&k_full[i], 1);
-      mbar_init(&k_empty[i], 1);
+      mbar_init(&k_empty[i], n_qt);                     // one commit per MMA issuer
       mbar_init(&v_full[i], 1);
-      mbar_init(&v_empty[i], 1);
+      mbar_init(&v_empty[i], n_qt);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < 4; ++i) {
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 4);
       mbar_init(&o_full[i], 1);
     }
+    for (int i = 0; i < 2; ++i) mbar_init(&qt_full[i], 4);
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == mma_warp) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0) {
+  if (warp == tma_warp) {
     // ================= TMA producer =================
     if (lane == 0) {
       mbar_expect_tx(q_full, n_qt * C::Q_BYTES);
       for (int t = 0; t < n_qt; ++t) {
         const int row = seq * p.Lq + q_row0 + t * BMQ;
 #pragma unroll
-        for (int c = 0; c < C::NCH; ++c) tma_load_3d(sQ + t * C::Q_BYTES + c * BMQ * 128, &tq, q_full, c * 64, h, row);
+        for (int c = 0; c < C::NCH; ++c) tma_load_3d((t ? sQ1 : sQ0) + c * BMQ * 128, &tq, q_full, c * 64, h, row);
       }
       int j = 0;
       for (int set = 0; set < p.n_sets; ++set) {
@@ -128,12 +180,14 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
           const int st = j % KV_STAGES;
           const uint32_t ph = (uint32_t)((j / KV_STAGES) & 1);
           const int row = kseq * p.Lk + kt * BNK;
-          mbar_wait(&k_empty[st], ph ^ 1);
+          if (C::ALIAS_Q && j == KV_STAGES - 1)          // first use of the stage that held Q: Q must be in TMEM
+            for (int t = 0; t < n_qt; ++t) mbar_wait_parked(&qt_full[t], 0, 2000);
+          mbar_wait_parked(&k_empty[st], ph ^ 1, 2000);
           mbar_expect_tx(&k_full[st], C::KV_BYTES);
 #pragma unroll
           for (int c = 0; c < C::NCH; ++c)
             tma_load_3d(sK + st * C::KV_BYTES + c * BNK * 128, &tk, &k_full[st], c * 64, h, row);
-          mbar_wait(&v_empty[st], ph ^ 1);
+          mbar_wait_parked(&v_empty[st], ph ^ 1, 2000);
           mbar_expect_tx(&v_full[st], C::KV_BYTES);
 #pragma unroll
           for (int c = 0; c < C::NCH; ++c)
@@ -141,54 +195,68 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
         }
       }
     }
-  } else if (warp == 1) {
-    // ================= MMA issuer =================
-    // The whole warp runs the warp-uniform control flow and one elected lane issues each tcgen05 instruction:
-    // descriptors then live in uniform registers and the MMAs of a tile go out back to back (with a lane-0
-    // branch the compiler wrapped every MMA in an R2UR + ELECT loop, ~50 clk per 40-64 clk MMA).  Every
-    // shared-memory descriptor is base + constant (the 14-bit address field never carries).
-    {
-      constexpr uint32_t idesc_qk = make_idesc_bf16(BMQ, BNK, 0, 0);
+  } else if (warp == 1 || warp == 10) {
+    // ================= MMA issuers: warp 1 -> query tile 0, warp 10 -> query tile 1 =================
+    // The whole warp runs the warp-uniform control flow and one elected lane issues each tcgen05 instruction
+    // (descriptors live in uniform registers; every shared-memory descriptor is base + constant, the 14-bit
+    // address field never carries).  One issuer per query tile: the chain  wait P -> P·V -> Q·K^T(next) -> commit
+    // of one tile costs ~700 clk per half-step, of which only ~400 is tensor-pipe time (MMAs that accumulate into
+    // the same TMEM tile issue in lock-step with their execution, tools/probes/mma_issue_probe.cu); with a single
+    // issuer the four chains of a step ran back to back and the softmax warps idled half of the time.
+    const int t = warp == 1 ? 0 : 1;
+    if (t < n_qt) {
+      constexpr uint32_t idesc_qk = make_idesc_bf16(BMQ, HB, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(BMQ, DP, 0, 1);     // A = P from TMEM, B = V is MN-major
-      const uint64_t dq0 = make_desc_k_sw128(smem_u32(sQ));
       const uint64_t dk0 = make_desc_k_sw128(smem_u32(sK));
       const uint64_t dv0 = make_desc_mn_sw128(smem_u32(sV), BNK * 128, 1024);
-      auto issue_qk = [&](int t, int st) {
-        const uint64_t da = dq0 + (uint64_t)(t * (C::Q_BYTES >> 4));
-        const uint64_t db = dk0 + (uint64_t)(st * (C::KV_BYTES >> 4));
+      const uint32_t s_tm = tmem_base + t * 128, o_tm = tmem_base + O_COL0 + t * 128, q_tm = tmem_base + Q_COL0 + t * 128;
+      // S_t^hf(j) = Q_t · K_j[hf·64 .. hf·64+63]^T  ->  TMEM columns t·128 + hf·64 .. +63.  A = Q_t from TMEM: an SS
+      // MMA would re-read the 4 KB Q slice from shared memory for every 64-key half and run at the 128 B/clk
+      // shared-memory limit (58 clk per 128x64x16 MMA measured, 32 clk of math)
+      auto issue_qk = [&](int hf, int st) {
+        const uint64_t db = dk0 + (uint64_t)(st * (C::KV_BYTES >> 4) + hf * ((HB * 128) >> 4));
 #pragma unroll
         for (int ks = 0; ks < DP / 16; ++ks) {
-          const uint64_t oa = (uint64_t)((ks / 4) * ((BMQ * 128) >> 4) + (ks % 4) * 2);
           const uint64_t ob = (uint64_t)((ks / 4) * ((BNK * 128) >> 4) + (ks % 4) * 2);
-          if (elect_one()) umma_bf16_ss(tmem_base + t * 128, da + oa, db + ob, idesc_qk, ks != 0);
+          if (elect_one()) umma_bf16_ts(s_tm + hf * HB, q_tm + ks * 8, db + ob, idesc_qk, ks != 0);
         }
-        if (elect_one()) umma_commit(&s_full[t]);
+        if (elect_one()) umma_commit(&s_full[t * 2 + hf]);
         __syncwarp();
       };
-      mbar_wait(q_full, 0);
+      mbar_wait(&qt_full[t], 0);
       mbar_wait(&k_full[0], 0);
       tc_fence_after();
-      for (int t = 0; t < n_qt; ++t) issue_qk(t, 0);
+      for (int hf = 0; hf < NH; ++hf) issue_qk(hf, 0);
       if (elect_one()) umma_commit(&k_empty[0]);
       __syncwarp();
       for (int j = 0; j < n_tiles; ++j) {
         const int st = j % KV_STAGES, st1 = (j + 1) % KV_STAGES;
         const bool more = j + 1 < n_tiles;
         const bool fresh = (j % n_kt) == 0;              // first tile of a K/V set: O starts over
-        mbar_wait(&v_full[st], (uint32_t)((j / KV_STAGES) & 1));
-        if (more) mbar_wait(&k_full[st1], (uint32_t)(((j + 1) / KV_STAGES) & 1));
+        const bool last_of_set = (j % n_kt) == n_kt - 1;
+        mbar_wait_parked(&v_full[st], (uint32_t)((j / KV_STAGES) & 1), 1000);
+        if (more) mbar_wait_parked(&k_full[st1], (uint32_t)(((j + 1) / KV_STAGES) & 1), 1000);
         const uint64_t dv = dv0 + (uint64_t)(st * (C::KV_BYTES >> 4));
-        for (int t = 0; t < n_qt; ++t) {
-          mbar_wait(&p_full[t], (uint32_t)(j & 1));
+        mark(j, 0);
+        for (int hf = 0; hf < NH; ++hf) {
+          mbar_wait_parked(&p_full[t * 2 + hf], (uint32_t)(j & 1), 1000);
           tc_fence_after();
+          mark(j, 1 + 2 * hf);
+          // O_t += P_t^hf · V_j[hf·64 ..]: P^hf sits on the first 32 columns of S_t^hf
 #pragma unroll
-          for (int ks = 0; ks < BNK / 16; ++ks)
+          for (int ks = 0; ks < HB / 16; ++ks)
             if (elect_one())
-              umma_bf16_ts(tmem_base + O_COL0 + t * 128, tmem_base + t * 128 + ks * 8,
-                           dv + (uint64_t)(ks * ((16 * 128) >> 4)), idesc_pv, (ks != 0) || !fresh);
-          if (elect_one()) umma_commit(&o_full[t]);
-          __syncwarp();
-          if (more) issue_qk(t, st1);
+              umma_bf16_ts(o_tm, s_tm + hf * HB + ks * 8, dv + (uint64_t)((hf * HB + ks * 16) * 128 >> 4), idesc_pv,
+                           (ks != 0) || (hf != 0) || !fresh);
+          // O is only read back at the end of a K/V set; in between, "P·V of a half-step has completed" is implied by
+          // the completion of the Q·K^T issued behind it (s_full), so the extra commit (~100 clk of this warp's
+          // issue chain each) is only spent on the last tile of a set
+          if (last_of_set) {
+            if (elect_one()) umma_commit(&o_full[t * 2 + hf]);
+            __syncwarp();
+          }
+          if (more) issue_qk(hf, st1);                   // S_t^hf(j+1) over the P it just consumed (in-order pipe)
+          mark(j, 2 + 2 * hf);
         }
         if (elect_one()) {
           umma_commit(&v_empty[st]);
@@ -197,7 +265,7 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
         __syncwarp();
       }
     }
-  } else if (((warp - 2) >> 2) < n_qt) {
+  } else if (warp < 10 && ((warp - 2) >> 2) < n_qt) {
     // ================= softmax warps: thread = query row =================
     const int t = (warp - 2) >> 2;
     const int quarter = warp & 3;                      // TMEM lane quarter this warp may touch
@@ -207,78 +275,142 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     const int q_idx = q_row0 + t * BMQ + row;
     const float c = p.scale_log2;
     bf16* orow = p.out + ((int64_t)seq * p.Lq + q_idx) * p.ldo + (int64_t)h * p.D;
+    {
+      // Q_t: this thread's row from the 128-byte-swizzled TMA tile (16-byte unit u of row r sits at u ^ (r % 8))
+      // -> TMEM columns Q_COL0 + 128·t .. (+ DP/2), the A-operand layout (lane = row, bf16 pairs along K)
+      mbar_wait(q_full, 0);
+      uint32_t qw[DP / 2];
+      const uint8_t* qrow = (t ? sQ1 : sQ0) + (row >> 3) * 1024 + (row & 7) * 128;
+#pragma unroll
+      for (int u = 0; u < DP / 8; ++u) {
+        const uint4 v4 = *reinterpret_cast<const uint4*>(qrow + (u >> 3) * (BMQ * 128) + (((u & 7) ^ (row & 7)) << 4));
+        qw[u * 4 + 0] = v4.x; qw[u * 4 + 1] = v4.y; qw[u * 4 + 2] = v4.z; qw[u * 4 + 3] = v4.w;
+      }
+      const uint32_t q_addr = lane_addr + Q_COL0 + t * 128;
+      tmem_st_x32(q_addr, qw);
+      if constexpr (DP / 2 > 32) tmem_st_x8(q_addr + 32, qw + 32);
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&qt_full[t]);
+    }
+    // The K/V tile is consumed in NH half-steps of 64 keys: while this warp runs the softmax of one half, the
+    // tensor core runs P·V of the previous half and Q·K^T of the same half of the NEXT tile, so S is (almost)
+    // always ready when the warp comes back for it and the exponentials never wait for the tensor pipe.
     int j = 0;
     for (int set = 0; set < p.n_sets; ++set) {
       float m_used = -INFINITY, l_run = 0.f;
       for (int kt = 0; kt < n_kt; ++kt, ++j) {
-        mbar_wait(&s_full[t], (uint32_t)(j & 1));
-        tc_fence_after();
-        uint32_t sr[BNK];
 #pragma unroll
-        for (int c0 = 0; c0 < BNK; c0 += 32) tmem_ld_x32(s_addr + c0, sr + c0);
-        tmem_ld_wait();
-        if (kt == n_kt - 1) {                          // ragged last tile: keys past Lk do not exist
-          const int kv_left = p.Lk - kt * BNK;
-          if (kv_left < BNK) {
+        for (int hf = 0; hf < NH; ++hf) {
+          const uint32_t sh_addr = s_addr + hf * HB;
+          mark(j * NH + hf, 0);
+          mbar_wait(&s_full[t * 2 + hf], (uint32_t)(j & 1));
+          tc_fence_after();
+          mark(j * NH + hf, 1);
+          uint32_t sr[HB];
+          auto load_s = [&]() {
+            tmem_ld_x32(sh_addr, sr);
+            tmem_ld_x32(sh_addr + 32, sr + 32);
+            tmem_ld_wait();
+            if (kt == n_kt - 1) {                        // ragged last tile: keys past Lk do not exist
+              const int kv_left = p.Lk - kt * BNK - hf * HB;
+              if (kv_left < HB) {
 #pragma unroll
-            for (int i = 0; i < BNK; ++i)
-              if (i >= kv_left) sr[i] = 0xff800000u;   // -inf
+                for (int i = 0; i < HB; ++i)
+                  if (i >= kv_left) sr[i] = 0xff800000u;  // -inf
+              }
+            }
+          };
+          load_s();
+          mark(j * NH + hf, 2);
+          // One pass over the half row: p = 2^(s·c − m_used·c) against the STALE reference maximum while the
+          // maximum of these 64 scores is reduced alongside (FMNMX3 in the shadow of the exponentials).  Only when
+          // it outgrows the reference by more than 2^RESCALE_LOG2 (or on the first half-step of a set, where there
+          // is no reference yet) is the reference moved, O rescaled in TMEM and the pass repeated.  PF of every 8
+          // pairs take the polynomial 2^x on the FMA pipe instead of MUFU.EX2 (16/clk/SM: the tightest unit at D=72).
+          uint32_t pk[HB / 2];
+          float l_tile, m_tile;
+          auto exp_pass = [&](float moff) {
+            const float2 c2 = make_float2(c, c), nm2 = make_float2(-moff, -moff);
+            float2 la = make_float2(0.f, 0.f), lb = make_float2(0.f, 0.f);
+            float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < HB; i += 4) {
+              const float s0 = __uint_as_float(sr[i]), s1 = __uint_as_float(sr[i + 1]);
+              const float s2 = __uint_as_float(sr[i + 2]), s3 = __uint_as_float(sr[i + 3]);
+              mx0 = fmax3(mx0, s0, s1);
+              mx1 = fmax3(mx1, s2, s3);
+              const float2 x01 = ffma2(make_float2(s0, s1), c2, nm2);
+              const float2 x23 = ffma2(make_float2(s2, s3), c2, nm2);
+              float2 e01, e23;
+              if (poly_pair(i / 2, PF)) e01 = ex2_poly2(x01);
+              else e01 = make_float2(ex2(x01.x), ex2(x01.y));
+              if (poly_pair(i / 2 + 1, PF)) e23 = ex2_poly2(x23);
+              else e23 = make_float2(ex2(x23.x), ex2(x23.y));
+              la = fadd2(la, e01);
+              lb = fadd2(lb, e23);
+              __nv_bfloat162 b01 = __floats2bfloat162_rn(e01.x, e01.y), b23 = __floats2bfloat162_rn(e23.x, e23.y);
+              pk[i / 2] = *reinterpret_cast<uint32_t*>(&b01);
+              pk[i / 2 + 1] = *reinterpret_cast<uint32_t*>(&b23);
+            }
+            l_tile = (la.x + la.y) + (lb.x + lb.y);
+            m_tile = fmaxf(mx0, mx1);
+          };
+          const bool first = kt == 0 && hf == 0;
+          if (first) {                                   // no reference yet: find the maximum first
+            float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < HB; i += 4) {
+              mx0 = fmax3(mx0, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]));
+              mx1 = fmax3(mx1, __uint_as_float(sr[i + 2]), __uint_as_float(sr[i + 3]));
+            }
+            m_used = fmaxf(mx0, mx1);
+            l_run = 0.f;
           }
-        }
-        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+          if constexpr (TRACE) asm volatile("" ::"f"(m_used) : "memory");
+          mark(j * NH + hf, 3);
+          exp_pass(m_used * c);
+          if (!first) {
+            const bool grow = (m_tile - m_used) * c > RESCALE_LOG2;
+            if (__any_sync(0xffffffffu, grow)) {
+              const float alpha = grow ? ex2((m_used - m_tile) * c) : 1.f;
+              if (grow) m_used = m_tile;
+              l_run *= alpha;
+              // rescale the running output in TMEM: P·V of the previous half-step must have completed; the next
+              // one is not issued before this warp arrives on p_full below.  The tensor pipe completes in issue
+              // order, so the Q·K^T that was issued right behind that P·V (its s_full phase) stands in for it;
+              // only the very last tile has no Q·K^T behind it and uses the end-of-set o_full commit.
+              if (hf == 0) mbar_wait(&s_full[t * 2 + NH - 1], (uint32_t)(j & 1));          // behind P·V^{last}(j-1)
+              else if (j + 1 < n_tiles) mbar_wait(&s_full[t * 2 + hf - 1], (uint32_t)((j + 1) & 1));  // behind P·V^{hf-1}(j)
+              else mbar_wait(&o_full[t * 2 + hf - 1], (uint32_t)(set & 1));
+              tc_fence_after();
 #pragma unroll
-        for (int i = 0; i < BNK; i += 4) {
-          mx0 = fmaxf(mx0, __uint_as_float(sr[i]));
-          mx1 = fmaxf(mx1, __uint_as_float(sr[i + 1]));
-          mx2 = fmaxf(mx2, __uint_as_float(sr[i + 2]));
-          mx3 = fmaxf(mx3, __uint_as_float(sr[i + 3]));
-        }
-        const float m_new = fmaxf(m_used, fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)));
-        const bool grow = (m_new - m_used) * c > RESCALE_LOG2;          // true on the first tile (m_used = -inf)
-        if (__any_sync(0xffffffffu, grow)) {
-          const float alpha = grow ? ex2((m_used - m_new) * c) : 1.f;  // 0 on the first tile
-          if (grow) m_used = m_new;
-          l_run *= alpha;
-          if (kt > 0) {
-            // rescale the running output in TMEM: PV(j-1) must have completed; PV(j) is not issued
-            // before this warp arrives on p_full below
-            mbar_wait(&o_full[t], (uint32_t)((j - 1) & 1));
-            tc_fence_after();
+              for (int c0 = 0; c0 < DP; c0 += 16) {
+                uint32_t r[16];
+                tmem_ld_x16(o_addr + c0, r);
+                tmem_ld_wait();
 #pragma unroll
-            for (int c0 = 0; c0 < DP; c0 += 16) {
-              uint32_t r[16];
-              tmem_ld_x16(o_addr + c0, r);
-              tmem_ld_wait();
-#pragma unroll
-              for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-              tmem_st_x16(o_addr + c0, r);
+                for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+                tmem_st_x16(o_addr + c0, r);
+              }
+              load_s();                                  // S is still in TMEM (P is stored below); the registers
+              exp_pass(m_used * c);                      // were recycled.  Rows that did not grow reproduce P.
             }
           }
+          l_run += l_tile;
+          if constexpr (TRACE) asm volatile("" ::"f"(l_run), "r"(pk[HB / 2 - 1]) : "memory");
+          mark(j * NH + hf, 4);
+          tmem_st_x32(sh_addr, pk);
+          tmem_st_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&p_full[t * 2 + hf]);
+          mark(j * NH + hf, 5);
         }
-        const float moff = m_used * c;
-        float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
-        uint32_t pk[BNK / 2];
-#pragma unroll
-        for (int i = 0; i < BNK; i += 4) {
-          const float e0 = ex2(fmaf(__uint_as_float(sr[i]), c, -moff));
-          const float e1 = ex2(fmaf(__uint_as_float(sr[i + 1]), c, -moff));
-          const float e2 = ex2(fmaf(__uint_as_float(sr[i + 2]), c, -moff));
-          const float e3 = ex2(fmaf(__uint_as_float(sr[i + 3]), c, -moff));
-          l0 += e0; l1 += e1; l2 += e2; l3 += e3;
-          __nv_bfloat162 b01 = __floats2bfloat162_rn(e0, e1), b23 = __floats2bfloat162_rn(e2, e3);
-          pk[i / 2] = *reinterpret_cast<uint32_t*>(&b01);
-          pk[i / 2 + 1] = *reinterpret_cast<uint32_t*>(&b23);
-        }
-        l_run += (l0 + l1) + (l2 + l3);
-#pragma unroll
-        for (int c0 = 0; c0 < BNK / 2; c0 += 32) tmem_st_x32(s_addr + c0, pk + c0);
-        tmem_st_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&p_full[t]);
         if (kt == n_kt - 1) {
           // end of a K/V set: normalise, round to bf16, add to what earlier sets left in `out`
-          mbar_wait(&o_full[t], (uint32_t)(j & 1));
+          mbar_wait(&o_full[t * 2 + NH - 1], (uint32_t)(set & 1));
           tc_fence_after();
           const float inv = 1.f / l_run;
 #pragma unroll
@@ -299,11 +431,11 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
                   if (set > 0) {
                     Vec16<bf16> prev;
                     prev.raw = *reinterpret_cast<const uint4*>(orow + d);
-                    float g[8], a[8];
-                    prev.unpack(g);
+                    float gg[8], a[8];
+                    prev.unpack(gg);
                     o.unpack(a);
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) a[i] += g[i];
+                    for (int i = 0; i < 8; ++i) a[i] += gg[i];
                     o.pack(a);
                   }
                   *reinterpret_cast<uint4*>(orow + d) = o.raw;
@@ -318,19 +450,21 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == mma_warp) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
-template <int DP, int BNK>
+long long* g_attn_trace = nullptr;
+
+template <int DP, int BNK, int PF = 0, bool TRACE = false>
 int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p, int n_seq,
                 cudaStream_t st) {
   using C = ACfg<DP, BNK>;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(attn_sm100_kernel<DP, BNK>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    cudaError_t e = cudaFuncSetAttribute(attn_sm100_kernel<DP, BNK, PF, TRACE>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
     if (e != cudaSuccess) {
       mdv2_set_error("attention_sm100: cannot set %d B dynamic smem: %s", C::SMEM, cudaGetErrorString(e));
       return MDV2_ECUDA;
@@ -338,11 +472,14 @@ int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap&
     configured = true;
   }
   dim3 grid((p.Lq + 2 * BMQ - 1) / (2 * BMQ), p.H, n_seq);
-  attn_sm100_kernel<DP, BNK><<<grid, NTHREADS, C::SMEM, st>>>(tq, tk, tv, p);
+  attn_sm100_kernel<DP, BNK, PF, TRACE><<<grid, NTHREADS, C::SMEM, st>>>(tq, tk, tv, p);
   MDV2_CHECK_LAUNCH("attention_sm100");
   return MDV2_OK;
 }
 }  // namespace
+
+// debug hook (not part of include/mdv2.h): device buffer of 10 x TRACE_STEPS x TRACE_EV int64 clock samples
+extern "C" void mdv2_debug_attn_trace(void* buf) { g_attn_trace = (long long*)buf; }
 
 bool mdv2_attention_sm100_supported(int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int Lq, int Lk, int H, int D,
                                     int n_sets) {
@@ -374,9 +511,29 @@ int mdv2_attention_sm100(const void* q, int64_t ldq, const void* k, int64_t ldk,
   p.Lq = Lq; p.Lk = Lk; p.H = H; p.D = D; p.n_sets = n_sets;
   p.scale_log2 = scale * 1.4426950408889634f;
   p.kv_map = kv_map;
+  p.trace = g_attn_trace;
+  static const int dbg = [] {
+    const char* e = getenv("MDV2_ATTN_DBG");
+    return e ? atoi(e) : 0;
+  }();
+  p.dbg = dbg;
+  static const int pf = [] {                             // tuning hook: polynomial pairs per 8 (tools/bench_attn.py)
+    const char* e = getenv("MDV2_ATTN_PF");
+    return e ? atoi(e) : ATTN_PF_DEFAULT;
+  }();
+  if (D == 72 && bnk == 128 && g_attn_trace) {
+    if (pf == 0) return launch_attn<80, 128, 0, true>(tq, tk, tv, p, n_seq, st);
+    return launch_attn<80, 128, ATTN_PF_DEFAULT ? ATTN_PF_DEFAULT : 3, true>(tq, tk, tv, p, n_seq, st);
+  }
   if (D == 72) {
     if (bnk == 64) return launch_attn<80, 64>(tq, tk, tv, p, n_seq, st);
-    return launch_attn<80, 128>(tq, tk, tv, p, n_seq, st);
+    switch (pf) {
+      case 0: return launch_attn<80, 128, 0>(tq, tk, tv, p, n_seq, st);
+      case 2: return launch_attn<80, 128, 2>(tq, tk, tv, p, n_seq, st);
+      case 3: return launch_attn<80, 128, 3>(tq, tk, tv, p, n_seq, st);
+      case 4: return launch_attn<80, 128, 4>(tq, tk, tv, p, n_seq, st);
+      default: MDV2_REQUIRE(false, "attention_sm100: MDV2_ATTN_PF must be 0, 2, 3 or 4");
+    }
   }
   if (bnk == 64) return launch_attn<64, 64>(tq, tk, tv, p, n_seq, st);
   return launch_attn<64, 128>(tq, tk, tv, p, n_seq, st);

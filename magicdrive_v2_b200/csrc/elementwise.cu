@@ -18,81 +18,137 @@ extern "C" const char* mdv2_last_kernel(void) { return g_kernel; }
 extern "C" int mdv2_version(void) { return MDV2_VERSION; }
 
 // ------------------------------------------------------------------------------------------------
-// LayerNorm -> modulate.  One warp per row; the row lives in registers (VPL 16-byte vectors/lane).
+// LayerNorm -> modulate.  One warp per row, the row lives in registers (VPL 16-byte vectors/lane).
+// A CTA owns LN_ROWS consecutive rows (warp w: rows w, w+8, ...).  The shift / (1+scale) rows of the
+// modulation table that its first row maps to are staged in shared memory once (every row of a (b,t)
+// frame shares them; fetching them per row from L2 cost 4x the activation bytes), rows of another
+// frame (a CTA straddling a frame boundary) read the table from global memory.  The next row's
+// vectors are requested before the current row is reduced, so every warp keeps two rows in flight.
 // ------------------------------------------------------------------------------------------------
+constexpr int LN_WARPS = 8, LN_ROWS = 64;
+
 template <typename T, int VPL>
-__global__ void __launch_bounds__(256) ln_modulate_kernel(const T* __restrict__ x, T* __restrict__ out,
-                                                          const float* __restrict__ mod, int64_t n_rows,
-                                                          int C, int K, int k_shift, int k_scale, int Tn,
-                                                          int S, int NC, float eps) {
+__global__ void __launch_bounds__(LN_WARPS * 32, VPL <= 5 ? 3 : 1) ln_modulate_kernel(const T* __restrict__ x, T* __restrict__ out,
+                                                                   const float* __restrict__ mod, uint32_t n_rows,
+                                                                   int C, int K, int k_shift, int k_scale,
+                                                                   uint32_t Tn, uint32_t S, uint32_t NC, float eps) {
   constexpr int VN = Vec16<T>::N;
-  const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (row >= n_rows) return;
+  extern __shared__ float s_tab[];                       // [0,C): shift, [C,2C): 1 + scale
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t row0 = blockIdx.x * LN_ROWS;
+  const uint32_t row_end = min(row0 + (uint32_t)LN_ROWS, n_rows);
   const int nvec = C / VN;
-  const Vec16<T>* xr = reinterpret_cast<const Vec16<T>*>(x + row * C);
-  float v[VPL][VN];
-  float sum = 0.f;
-#pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    int vi = lane + 32 * i;
-    if (vi < nvec) {
-      Vec16<T> t = xr[vi];
-      t.unpack(v[i]);
-#pragma unroll
-      for (int j = 0; j < VN; ++j) sum += v[i][j];
+  auto table_row = [&](uint32_t r) {
+    const uint32_t g = r / S;
+    return (g / Tn / NC) * Tn + g % Tn;
+  };
+  const uint32_t tab0 = table_row(row0);
+  {
+    const float* mrow = mod + (int64_t)tab0 * K * C;
+    const float4* sh4 = reinterpret_cast<const float4*>(mrow + (int64_t)k_shift * C);
+    const float4* sc4 = reinterpret_cast<const float4*>(mrow + (int64_t)k_scale * C);
+    for (int i = threadIdx.x; i < C / 4; i += LN_WARPS * 32) {
+      reinterpret_cast<float4*>(s_tab)[i] = sh4[i];
+      float4 sc = sc4[i];
+      sc.x += 1.f; sc.y += 1.f; sc.z += 1.f; sc.w += 1.f;
+      reinterpret_cast<float4*>(s_tab + C)[i] = sc;
     }
   }
-  const float mean = warp_sum(sum) / C;
-  float sq = 0.f;
+  Vec16<T> cur[VPL], nxt[VPL];
+  auto load_row = [&](uint32_t r, Vec16<T>* dst) {
+    const Vec16<T>* xr = reinterpret_cast<const Vec16<T>*>(x + (int64_t)r * C);
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    if (lane + 32 * i < nvec) {
+    for (int i = 0; i < VPL; ++i) {
+      const int vi = lane + 32 * i;
+      if (vi < nvec) dst[i] = xr[vi];
+    }
+  };
+  uint32_t row = row0 + warp;
+  if (row < row_end) load_row(row, nxt);
+  __syncthreads();
+  for (; row < row_end; row += LN_WARPS) {
 #pragma unroll
-      for (int j = 0; j < VN; ++j) {
-        float dlt = v[i][j] - mean;
-        sq += dlt * dlt;
+    for (int i = 0; i < VPL; ++i) cur[i] = nxt[i];
+    if (row + LN_WARPS < row_end) load_row(row + LN_WARPS, nxt);
+    // the row stays PACKED in registers (cur) and is unpacked once per pass: three cheap unpacks instead of
+    // 8 live fp32 values per vector keep the kernel at 4 CTAs/SM
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      if (lane + 32 * i < nvec) {
+        float v[VN];
+        cur[i].unpack(v);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) sum += v[j];
       }
     }
-  }
-  const float rstd = rsqrtf(warp_sum(sq) / C + eps);
-  const float* mrow = mod + mod_row(row, Tn, S, NC) * (int64_t)K * C;
-  const float* sh = mrow + (int64_t)k_shift * C;
-  const float* sc = mrow + (int64_t)k_scale * C;
-  Vec16<T>* orow = reinterpret_cast<Vec16<T>*>(out + row * C);
+    const float mean = warp_sum(sum) / C;
+    float sq = 0.f;
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    int vi = lane + 32 * i;
-    if (vi < nvec) {
-      float o[VN];
+    for (int i = 0; i < VPL; ++i) {
+      if (lane + 32 * i < nvec) {
+        float v[VN];
+        cur[i].unpack(v);
 #pragma unroll
-      for (int j = 0; j < VN; j += 4) {
-        float4 s4 = *reinterpret_cast<const float4*>(sc + vi * VN + j);
-        float4 h4 = *reinterpret_cast<const float4*>(sh + vi * VN + j);
-        o[j + 0] = (v[i][j + 0] - mean) * rstd * (1.f + s4.x) + h4.x;
-        o[j + 1] = (v[i][j + 1] - mean) * rstd * (1.f + s4.y) + h4.y;
-        o[j + 2] = (v[i][j + 2] - mean) * rstd * (1.f + s4.z) + h4.z;
-        o[j + 3] = (v[i][j + 3] - mean) * rstd * (1.f + s4.w) + h4.w;
+        for (int j = 0; j < VN; ++j) {
+          const float dlt = v[j] - mean;
+          sq += dlt * dlt;
+        }
       }
-      Vec16<T> t;
-      t.pack(o);
-      orow[vi] = t;
+    }
+    const float rstd = rsqrtf(warp_sum(sq) / C + eps);
+    const uint32_t tab = table_row(row);
+    const bool staged = tab == tab0;
+    const float* mrow = mod + (int64_t)tab * K * C;
+    const float* gsh = mrow + (int64_t)k_shift * C;
+    const float* gsc = mrow + (int64_t)k_scale * C;
+    Vec16<T>* orow = reinterpret_cast<Vec16<T>*>(out + (int64_t)row * C);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      const int vi = lane + 32 * i;
+      if (vi < nvec) {
+        float o[VN], v[VN];
+        cur[i].unpack(v);
+#pragma unroll
+        for (int j = 0; j < VN; j += 4) {
+          float4 s4, h4;
+          if (staged) {
+            h4 = *reinterpret_cast<const float4*>(s_tab + vi * VN + j);
+            s4 = *reinterpret_cast<const float4*>(s_tab + C + vi * VN + j);
+          } else {
+            h4 = *reinterpret_cast<const float4*>(gsh + vi * VN + j);
+            s4 = *reinterpret_cast<const float4*>(gsc + vi * VN + j);
+            s4.x += 1.f; s4.y += 1.f; s4.z += 1.f; s4.w += 1.f;
+          }
+          o[j + 0] = (v[j + 0] - mean) * rstd * s4.x + h4.x;
+          o[j + 1] = (v[j + 1] - mean) * rstd * s4.y + h4.y;
+          o[j + 2] = (v[j + 2] - mean) * rstd * s4.z + h4.z;
+          o[j + 3] = (v[j + 3] - mean) * rstd * s4.w + h4.w;
+        }
+        Vec16<T> t;
+        t.pack(o);
+        orow[vi] = t;
+      }
     }
   }
 }
 
 template <typename T>
-static int launch_ln_modulate(const void* x, void* out, const float* mod, int64_t n_rows, int C, int K,
-                              int ks, int kc, int T_, int S, int NC, float eps, cudaStream_t st) {
+static int launch_ln_modulate(const void* x, void* out, const float* mod, int64_t n_rows, int C, int K, int ks,
+                              int kc, int T_, int S, int NC, float eps, cudaStream_t st) {
   constexpr int VN = Vec16<T>::N;
   MDV2_REQUIRE(C % VN == 0, "ln_modulate: C=%d must be a multiple of %d", C, VN);
+  MDV2_REQUIRE(n_rows < (1ll << 31), "ln_modulate: too many rows");
+  MDV2_REQUIRE(((uintptr_t)x % 16 == 0) && ((uintptr_t)out % 16 == 0) && ((uintptr_t)mod % 16 == 0),
+               "ln_modulate: operands must be 16-byte aligned");
   const int nvec = C / VN;
   const int vpl = (nvec + 31) / 32;
-  const int wpb = 8;
-  dim3 grid((unsigned)((n_rows + wpb - 1) / wpb)), block(wpb * 32);
-#define LN_CASE(V)                                                                                    \
-  ln_modulate_kernel<T, V><<<grid, block, 0, st>>>((const T*)x, (T*)out, mod, n_rows, C, K, ks, kc, T_, \
-                                                   S, NC, eps)
+  const size_t smem = 2 * (size_t)C * sizeof(float);
+  MDV2_REQUIRE(smem <= 48 * 1024, "ln_modulate: C=%d too large", C);
+  dim3 grid((unsigned)((n_rows + LN_ROWS - 1) / LN_ROWS)), block(LN_WARPS * 32);
+#define LN_CASE(V)                                                                                             \
+  ln_modulate_kernel<T, V><<<grid, block, smem, st>>>((const T*)x, (T*)out, mod, (uint32_t)n_rows, C, K, ks, kc, \
+                                                      (uint32_t)T_, (uint32_t)S, (uint32_t)NC, eps)
   if (vpl <= 2) LN_CASE(2);
   else if (vpl <= 5) LN_CASE(5);
   else if (vpl <= 10) LN_CASE(10);

@@ -9,6 +9,7 @@
 // warp 0 = TMA producer, warp 1 = MMA issuer (leader) + TMEM owner, warps 2-9 = epilogue (TMEM ->
 // registers -> fused bias / per-head RMSNorm / GELU -> shared staging -> gate / residual -> coalesced
 // stores).  Two TMEM accumulator stages let the epilogue of tile i overlap the main loop of tile i+1.
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -26,16 +27,19 @@ constexpr int TMEM_COLS = 512, ACC_STRIDE = 256;
 
 template <int BN, int HD>
 struct Cfg {
-  static constexpr int CW = HD ? HD : 64;                // epilogue chunk width (columns)
+  static constexpr int CW = HD ? HD : 32;                // epilogue chunk width (columns)
+  static constexpr int CPW = BN / CW / 2;                // chunks per epilogue warp and tile (column halves interleave)
   static constexpr int B_BYTES = (BN / 2) * BK * 2;      // this CTA's half of the W tile
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int PITCH = ((CW * 2 / 16) % 2 == 1) ? CW * 2 : CW * 2 + 16;   // odd multiple of 16 B
-  static constexpr int EPW = 32 * PITCH + 512 + 320;       // per warp: staging + row info + bias (fp32)
+  static constexpr int EPW = 32 * PITCH + 512 + CPW * CW * 4;   // per warp: staging + row info + bias (fp32)
   static constexpr int STAGING = NUM_EPI_WARPS * EPW;
-  static constexpr int STAGES_RAW = (232448 - 1024 - 256 - STAGING) / STAGE_BYTES;
+  static constexpr int RMSW = HD ? 2 * HD * 4 : 0;       // q / k RMSNorm weights (fp32), staged once
+  static constexpr int STAGES_RAW = (232448 - 1024 - 256 - STAGING - RMSW) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
-  static constexpr int SMEM = STAGES * STAGE_BYTES + STAGING + 256 + 1024;  // + barriers + align slack
-  static_assert(BN % CW == 0, "tile must hold whole epilogue chunks");
+  static constexpr int SMEM = STAGES * STAGE_BYTES + STAGING + RMSW + 256 + 1024;  // + barriers + align slack
+  static_assert(BN % (2 * CW) == 0, "every epilogue warp takes the same number of chunks");
+  static_assert(EPW % 16 == 0, "per-warp staging must stay 16-byte aligned");
   static_assert((PITCH / 16) % 2 == 1, "staging pitch must be an odd multiple of 16 B");
   static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-B alignment");
 };
@@ -60,7 +64,8 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + C::STAGES * C::STAGE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::STAGING);
+  float* s_rms = reinterpret_cast<float*>(staging + C::STAGING);          // [2][HD]: q weights, k weights
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::STAGING + C::RMSW);
   uint64_t* full = bars;
   uint64_t* empty = bars + C::STAGES;
   uint64_t* tfull = bars + 2 * C::STAGES;
@@ -89,8 +94,14 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc_pair(tmem_slot, TMEM_COLS);
+  if constexpr (HD != 0) {
+    for (int i = threadIdx.x; i < 2 * HD; i += NUM_THREADS) {
+      const bf16* w = i < HD ? p.rms_q : p.rms_k;
+      s_rms[i] = w ? __bfloat162float(w[i % HD]) : 1.f;
+    }
+  }
   tc_fence_before();
-  cluster_sync();                                        // barriers + TMEM of both CTAs are ready
+  cluster_sync();                                        // barriers + TMEM of both CTAs are ready (and s_rms)
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -141,60 +152,111 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
   } else {
     // ===== epilogue warps: TMEM lane quarter = warp % 4, column chunks ch ≡ half (mod 2) =====
-    constexpr int CW = C::CW;
+    // Everything the epilogue reads from global memory is requested BEFORE it is needed: the bias of all of the
+    // warp's chunks goes to shared memory ahead of the accumulator wait, and the residual / gate vectors of
+    // chunk i+1 are loaded into registers before chunk i is processed (a dependent load per 16-byte store had
+    // the K = 1152 GEMMs with gate + residual running at 24 % tensor-pipe activity, ncu profiles/).
+    constexpr int CW = C::CW, CPW = C::CPW;
     constexpr int UPR = CW / 8;                       // 16-byte units per staged row
+    constexpr int NIT = UPR;                          // column-phase iterations: 32 rows x UPR units / 32 lanes
+    constexpr bool FIXED_U = (32 % UPR) == 0;         // lane -> constant column unit (gate vector reused over rows)
     const int quarter = warp & 3;
     const int half = (warp - 2) >> 2;
     uint8_t* stg = staging + (warp - 2) * C::EPW;
     int64_t* row_res = reinterpret_cast<int64_t*>(stg + 32 * C::PITCH);
     int64_t* row_gate = row_res + 32;
-    float* sbias = reinterpret_cast<float*>(row_gate + 32);
+    float* sbias = reinterpret_cast<float*>(row_gate + 32);   // [CPW][CW]
     int acc = 0;
     uint32_t acc_phase = 0;
     const Epilogue<bf16>& ep = p.ep;
+    // the RMSNorm flavour (qkv projections) never carries a gate or a residual (api.cu rejects the combination)
+    const bool has_res = HD == 0 && ep.res != nullptr, has_gate = HD == 0 && ep.gate_mod != nullptr;
     for (int64_t tile = pair; tile < n_tiles; tile += n_pairs) {
       const int64_t m0 = (tile / n_tiles_n) * 2 * BM + (int64_t)rank * BM;
       const int n0 = (int)(tile % n_tiles_n) * BN;
+      const int64_t r0 = m0 + quarter * 32;          // first row of this warp
       {  // per-row epilogue context, once per tile (64-bit divisions stay out of the inner loops)
-        const int64_t gr = m0 + quarter * 32 + lane;
+        const int64_t gr = r0 + lane;
         const RowCtx rc = ep.row_ctx(gr < p.M ? gr : 0);
         row_res[lane] = rc.res_row * ep.ldr;
         row_gate[lane] = rc.gate ? (int64_t)(rc.gate - ep.gate_mod) : -1;
       }
+#pragma unroll
+      for (int ci = 0; ci < CPW; ++ci) {
+        const int c0 = n0 + (half + 2 * ci) * CW;
+        for (int jj = lane; jj < CW; jj += 32)
+          sbias[ci * CW + jj] = ep.bias ? ep.bias_scale * __bfloat162float(ep.bias[c0 + jj]) : 0.f;
+      }
+      __syncwarp();
+      const bool gate_uniform = FIXED_U && has_gate && row_gate[0] == row_gate[31];
+      // residual / gate registers of one chunk (lane: rows rl = idx / UPR, unit u = idx % UPR, idx = lane + 32 it)
+      uint4 rres[NIT];
+      float4 rg0, rg1;
+      auto prefetch = [&](int ci) {
+        const int c0 = n0 + (half + 2 * ci) * CW;
+        if (has_res) {
+#pragma unroll
+          for (int it = 0; it < NIT; ++it) {
+            const int idx = lane + 32 * it, rl = idx / UPR, u = idx % UPR;
+            if (r0 + rl < p.M) rres[it] = *reinterpret_cast<const uint4*>(ep.res + row_res[rl] + c0 + u * 8);
+          }
+        }
+        if (gate_uniform) {
+          const float* g = ep.gate_mod + row_gate[0] + c0 + (lane % UPR) * 8;
+          rg0 = *reinterpret_cast<const float4*>(g);
+          rg1 = *reinterpret_cast<const float4*>(g + 4);
+        }
+      };
+      prefetch(0);
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + acc * ACC_STRIDE + ((uint32_t)(quarter * 32) << 16);
 #pragma unroll 1
-      for (int ch = half; ch < BN / CW; ch += 2) {
+      for (int ci = 0; ci < CPW; ++ci) {
+        const int ch = half + 2 * ci;
         const int c0 = n0 + ch * CW;
         uint32_t raw[CW];
         tmem_ld_x32(t_row + ch * CW, raw);
-        tmem_ld_x32(t_row + ch * CW + 32, raw + 32);
+        if constexpr (CW >= 64) tmem_ld_x32(t_row + ch * CW + 32, raw + 32);
         if constexpr (CW == 72) tmem_ld_x8(t_row + ch * CW + 64, raw + 64);
-        // bias of this chunk -> smem (fp32) while the TMEM load is in flight
-        for (int jj = lane; jj < CW; jj += 32)
-          sbias[jj] = ep.bias ? ep.bias_scale * __bfloat162float(ep.bias[c0 + jj]) : 0.f;
-        __syncwarp();
+        // this chunk's residual / gate registers; the next chunk's loads go out before the TMEM data is consumed
+        uint4 cres[NIT];
+#pragma unroll
+        for (int it = 0; it < NIT; ++it) cres[it] = rres[it];
+        const float4 cg0 = rg0, cg1 = rg1;
+        if (ci + 1 < CPW) prefetch(ci + 1);
         tmem_ld_wait();
+        if (ci == CPW - 1) {                         // accumulator stage drained: the MMA warp may reuse it
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_leader(&tempty[acc]);
+        }
         float v[CW];
+        const float* sb = sbias + ci * CW;
 #pragma unroll
         for (int jj = 0; jj < CW; jj += 4) {
-          const float4 b4 = *reinterpret_cast<const float4*>(sbias + jj);
+          const float4 b4 = *reinterpret_cast<const float4*>(sb + jj);
           v[jj + 0] = __uint_as_float(raw[jj + 0]) + b4.x;
           v[jj + 1] = __uint_as_float(raw[jj + 1]) + b4.y;
           v[jj + 2] = __uint_as_float(raw[jj + 2]) + b4.z;
           v[jj + 3] = __uint_as_float(raw[jj + 3]) + b4.w;
         }
         if constexpr (HD != 0) {
-          const bf16* w = c0 < p.n_q ? p.rms_q : (c0 < p.n_q + p.n_k ? p.rms_k : nullptr);
-          if (w != nullptr) {
+          const int wsel = c0 < p.n_q ? 0 : (c0 < p.n_q + p.n_k ? 1 : 2);
+          if (wsel < 2) {
+            const float* w = s_rms + wsel * HD;
             float ss = 0.f;
 #pragma unroll
             for (int jj = 0; jj < CW; ++jj) ss += v[jj] * v[jj];
             const float r = rsqrtf(ss / CW + p.eps);
 #pragma unroll
-            for (int jj = 0; jj < CW; ++jj)
-              v[jj] = __bfloat162float(__ldg(w + jj)) * __bfloat162float(__float2bfloat16_rn(v[jj] * r));
+            for (int jj = 0; jj < CW; jj += 4) {
+              const float4 w4 = *reinterpret_cast<const float4*>(w + jj);
+              v[jj + 0] = w4.x * __bfloat162float(__float2bfloat16_rn(v[jj + 0] * r));
+              v[jj + 1] = w4.y * __bfloat162float(__float2bfloat16_rn(v[jj + 1] * r));
+              v[jj + 2] = w4.z * __bfloat162float(__float2bfloat16_rn(v[jj + 2] * r));
+              v[jj + 3] = w4.w * __bfloat162float(__float2bfloat16_rn(v[jj + 3] * r));
+            }
           }
         }
         if (ep.act == 1) {
@@ -211,27 +273,30 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         __syncwarp();
         // column phase: coalesced 16-byte accesses: gate / residual / store
-#pragma unroll 2
-        for (int idx = lane; idx < 32 * UPR; idx += 32) {
-          const int rl = idx / UPR, u = idx % UPR;
-          const int64_t gr = m0 + quarter * 32 + rl;
+#pragma unroll
+        for (int it = 0; it < NIT; ++it) {
+          const int idx = lane + 32 * it, rl = idx / UPR, u = idx % UPR;
+          const int64_t gr = r0 + rl;
           if (gr < p.M) {
             Vec16<bf16> pk;
             pk.raw = *reinterpret_cast<const uint4*>(stg + rl * C::PITCH + u * 16);
             const int col = c0 + u * 8;
-            const int64_t goff = row_gate[rl];
-            if (goff >= 0 || ep.res) {
+            if (has_gate || has_res) {
               float f[8];
               pk.unpack(f);
-              if (goff >= 0) {
-                const float4 g0 = *reinterpret_cast<const float4*>(ep.gate_mod + goff + col);
-                const float4 g1 = *reinterpret_cast<const float4*>(ep.gate_mod + goff + col + 4);
+              if (has_gate) {
+                float4 g0 = cg0, g1 = cg1;
+                if (!gate_uniform) {
+                  const int64_t goff = row_gate[rl];
+                  g0 = *reinterpret_cast<const float4*>(ep.gate_mod + goff + col);
+                  g1 = *reinterpret_cast<const float4*>(ep.gate_mod + goff + col + 4);
+                }
                 f[0] *= g0.x; f[1] *= g0.y; f[2] *= g0.z; f[3] *= g0.w;
                 f[4] *= g1.x; f[5] *= g1.y; f[6] *= g1.z; f[7] *= g1.w;
               }
-              if (ep.res) {
+              if (has_res) {
                 Vec16<bf16> rv;
-                rv.raw = *reinterpret_cast<const uint4*>(ep.res + row_res[rl] + col);
+                rv.raw = cres[it];
                 float rf[8];
                 rv.unpack(rf);
 #pragma unroll
@@ -244,9 +309,6 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         __syncwarp();
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_leader(&tempty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
@@ -350,6 +412,11 @@ int pick_bn(int N, const RmsArgs* rms) {
     if (rms->head_dim == 64 && N % 128 == 0) return 128;
     return 0;
   }
+  static const int forced = [] {                       // tuning hook for tools/bench_gemm.py
+    const char* e = getenv("MDV2_GEMM_BN");
+    return e ? atoi(e) : 0;
+  }();
+  if ((forced == 256 || forced == 192 || forced == 128 || forced == 64) && N % forced == 0) return forced;
   if (N % 256 == 0) return 256;
   if (N % 192 == 0) return 192;
   if (N % 128 == 0) return 128;

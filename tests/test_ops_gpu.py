@@ -187,10 +187,12 @@ def test_error_behaviour():
     o.gemm(e, rnd(64, 64, dtype=torch.bfloat16), None, torch.empty(0, 64, dtype=torch.bfloat16, device=DEV))
 
 
-def _attn_case(n_seq, Lq, Lk, H, D, *, kv="self", seed=0):
+def _attn_case(n_seq, Lq, Lk, H, D, *, kv="self", seed=0, q_gain=1.0):
     bf = torch.bfloat16
     C = H * D
     qkv = rnd(n_seq * Lq, 3 * C, dtype=bf, seed=seed + 1)
+    if q_gain != 1.0:
+        qkv[:, :C] *= q_gain
     q = qkv[:, :C]
     kv_map = None
     if kv == "cross":
@@ -226,6 +228,14 @@ def test_attention_tcgen05_cross_view_and_cross(D):
 
 def test_attention_tcgen05_xl_shape():
     assert _attn_case(12, 1400, 1400, 16, 72) < 2e-2
+
+
+@pytest.mark.parametrize("gain", [6.0, 20.0])
+def test_attention_tcgen05_rescale_path(gain):
+    """Scores with a spread of tens of log2 units: the running maximum keeps outgrowing the lazy-rescale
+    threshold, so the in-TMEM rescale of O and the repeated exponential pass are exercised on most tiles."""
+    assert _attn_case(4, 1000, 1000, 4, 72, q_gain=gain) < 2e-2
+    assert _attn_case(4, 600, 600, 4, 72, kv="xview", q_gain=gain) < 2e-2
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])

@@ -32,7 +32,23 @@ def bench(n_seq, Lq, Lk, H=16, D=72, kind="self", iters=5):
     fl = 4.0 * n_seq * Lq * Lk * H * D * n_sets
     print(f"{kind:6s} n_seq={n_seq:3d} Lq={Lq:5d} Lk={Lk:5d} D={D}: {ms:8.3f} ms  {fl / ms / 1e9:7.1f} TF/s (algorithmic, D un-padded)", flush=True)
 
+def accuracy(n_seq=2, L=1408, H=16, D=72):
+    """rel. L2 error against an fp32 softmax(QK^T)V of the same bf16 inputs."""
+    bf = torch.bfloat16
+    C = H * D
+    g = torch.Generator(device="cuda").manual_seed(1)
+    qkv = torch.randn(n_seq * L, 3 * C, device="cuda", dtype=bf, generator=g)
+    out = torch.empty(n_seq * L, C, device="cuda", dtype=bf)
+    ops.attention(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], out, n_seq, L, L, H, D, D ** -0.5)
+    q, k, v = (qkv[:, i * C:(i + 1) * C].float().view(n_seq, L, H, D).transpose(1, 2) for i in range(3))
+    ref = torch.softmax(q @ k.transpose(-1, -2) * D ** -0.5, dim=-1) @ v
+    ref = ref.transpose(1, 2).reshape(n_seq * L, C)
+    err = ((out.float() - ref).norm() / ref.norm()).item()
+    print(f"accuracy vs fp32 reference (n_seq={n_seq}, L={L}): rel L2 = {err:.3e}", flush=True)
+
+
 if __name__ == "__main__":
+    accuracy()
     bench(60, 5600, 5600, iters=int(os.environ.get("ITERS", "5")))
     if "--quick" not in sys.argv:
         bench(60, 5600, 5600, kind="xview")

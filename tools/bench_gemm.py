@@ -50,7 +50,46 @@ def sustained(M, N, K, secs=1.5, **kw):
     print(f"sustained M={M} N={N} K={K}: mdv2 {res['mdv2']:7.1f} TF  cublas {res['cublas']:7.1f} TF", flush=True)
 
 
+def model_cases(M=84000, iters=20):
+    """The five GEMM flavours of a block with their in-model epilogues (T=5, S=M/60... geometry of cfg3)."""
+    bf = torch.bfloat16
+    C = 1152
+    S = M // 60
+    geo = (5, S, 6)
+    mod = torch.randn(10, 6, C, device="cuda", dtype=torch.float32) * 0.1
+    qn = torch.ones(72, device="cuda", dtype=bf)
+    def run(name, N, K, **kw):
+        a = torch.randn(M, K, device="cuda", dtype=bf)
+        w = torch.randn(N, K, device="cuda", dtype=bf) * K ** -0.5
+        b = torch.randn(N, device="cuda", dtype=bf)
+        o = torch.randn(M, N, device="cuda", dtype=bf)
+        if kw.pop("inplace_res", False):
+            kw["res"] = o
+        fn = lambda: ops.gemm(a, w, b, o, backend="tcgen05", **kw)
+        for _ in range(3): fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters): fn()
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        print(f"{name:22s} M={M} N={N:5d} K={K:5d}: {ms:7.3f} ms {2.0 * M * N * K / ms / 1e9:7.1f} TF", flush=True)
+    run("proj  bias+gate+res", C, C, geo=geo, gate=(mod, 2), inplace_res=True)
+    run("q_lin bias", C, C)
+    run("fc2   bias+gate+res", C, 4 * C, geo=geo, gate=(mod, 5), inplace_res=True)
+    run("fc1   bias+gelu", 4 * C, C, act="gelu")
+    run("qkv   bias+rmsnorm", 3 * C, C, rms=(qn, qn, 72, C, C))
+
+
 if __name__ == "__main__":
+    if "--model" in sys.argv:
+        model_cases()
+        sys.exit(0)
+    if "--profile" in sys.argv:
+        torch.cuda.profiler.start()
+        model_cases(iters=1)
+        torch.cuda.profiler.stop()
+        sys.exit(0)
     if "--sustained" in sys.argv:
         for (N, K) in ((1152, 1152), (3456, 1152), (4608, 1152), (1152, 4608)):
             sustained(336000, N, K, backend="tcgen05")
