@@ -88,6 +88,17 @@ int mdv2_unpatchify(const void* y, float* out, int b, int NC, int Cout, int T, i
  * magicdrivedit/acceleration/communications.py:11-21 and the head/sequence rearranges of blocks.py:571-638. */
 int mdv2_swap01(const void* src, void* dst, int64_t A, int64_t B, int64_t inner_bytes, void* stream);
 
+/* Strided scatter of contiguous runs to up to 8 destination buffers (the ranks of a sequence-parallel group,
+ * mapped through NVLink peer memory): for every index (i0,i1,i2,i3) < sizes,
+ *   dst_ptrs[i_{peer_dim}] [dst_base + sum_{k != peer_dim} i_k·dst_strides[k] : +run_bytes]
+ *     = src[sum_k i_k·src_strides[k] : +run_bytes]            (strides and dst_base in bytes, all multiples of 16).
+ * One launch packs, transfers and un-packs a Ulysses all-to-all: it replaces the two all_to_all calls plus the
+ * split / cat / rearrange copies of magicdrivedit/acceleration/communications.py:11-66 and blocks.py:571-638.
+ * The caller orders it against the peers (a group barrier after the launch, before the data is consumed). */
+int mdv2_scatter_runs(const void* src, void* const* dst_ptrs, int n_dst, int peer_dim, const int64_t* sizes,
+                      const int64_t* src_strides, const int64_t* dst_strides, int64_t run_bytes, int64_t dst_base,
+                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif

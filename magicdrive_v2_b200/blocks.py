@@ -97,14 +97,22 @@ class STDiT3Block(nn.Module):
         scale = D ** -0.5
         qn, kn = getattr(a.q_norm, "weight", None), getattr(a.k_norm, "weight", None)
 
-        # (b) LN -> modulate ; (c) self-attention ; (d) gated residual
-        ops.ln_modulate(x, ws.xm, mod, 0, 1, geo)
-        ops.gemm(ws.xm, a.qkv.weight, a.qkv.bias, ws.qkv, geo=geo, rms=(qn, kn, D, C, C))
+        # (b) LN -> modulate ; (c) self-attention ; (d) gated residual.  The projections on either side of a
+        # spatial attention are handed over as row-range callbacks (see MagicDriveSTDiT3._spatial_attention).
+        def qkv_rows(rows, tab):
+            ops.ln_modulate(x[rows], ws.xm[rows], tab(mod), 0, 1, geo)
+            ops.gemm(ws.xm[rows], a.qkv.weight, a.qkv.bias, ws.qkv[rows], geo=geo, rms=(qn, kn, D, C, C))
+
+        def proj_rows(rows, tab):
+            ops.gemm(ws.ao[rows], a.proj.weight, a.proj.bias, x[rows], geo=geo, gate=(tab(mod), 2), res=x[rows])
+
         if self.temporal:
+            rows = slice(0, x.shape[0])
+            qkv_rows(rows, lambda m: m)
             ops.temporal_attention(ws.qkv, ctx.rope_cos, ctx.rope_sin, ws.ao, d.B, T, S, H, D, scale)
+            proj_rows(rows, lambda m: m)
         else:
-            ctx.spatial_attention(ops, ws.qkv, ws.ao, d, None, scale)
-        ops.gemm(ws.ao, a.proj.weight, a.proj.bias, x, geo=geo, gate=(mod, 2), res=x)
+            ctx.spatial_attention(ops, ws.qkv, ws.ao, d, None, scale, qkv_rows, proj_rows)
 
         # (e) cross-attention onto the condition tokens: un-normed, un-gated
         if not self.skip_cross_attn:
@@ -120,14 +128,20 @@ class STDiT3Block(nn.Module):
         # (f) cross-view attention (spatial base blocks): each view attends to its neighbours
         if not self.skip_cross_view:
             cv = self.cross_view_attn
-            ops.ln_modulate(x, ws.xm, mod_mva, 0, 1, geo)
-            ops.gemm(ws.xm, cv.qkv.weight, None, ws.qkv, geo=geo,
-                     rms=(cv.q_norm.weight, cv.k_norm.weight, D, C, C))
-            ctx.spatial_attention(ops, ws.qkv, ws.ao, d, ctx.kv_map, scale)
-            # proj(a0) + proj(a1) = W(a0 + a1) + n_nbr·bias ; then gate ; then mva_proj + residual
-            ops.gemm(ws.ao, cv.proj.weight, cv.proj.bias, ws.xm, geo=geo,
-                     bias_scale=float(ctx.kv_map.shape[1]), gate=(mod_mva, 2))
-            ops.gemm(ws.xm, self.mva_proj.weight, self.mva_proj.bias, x, geo=geo, res=x)
+            n_nbr = float(ctx.kv_map.shape[1])
+
+            def cv_qkv_rows(rows, tab):
+                ops.ln_modulate(x[rows], ws.xm[rows], tab(mod_mva), 0, 1, geo)
+                ops.gemm(ws.xm[rows], cv.qkv.weight, None, ws.qkv[rows], geo=geo,
+                         rms=(cv.q_norm.weight, cv.k_norm.weight, D, C, C))
+
+            def cv_proj_rows(rows, tab):
+                # proj(a0) + proj(a1) = W(a0 + a1) + n_nbr·bias ; then gate ; then mva_proj + residual
+                ops.gemm(ws.ao[rows], cv.proj.weight, cv.proj.bias, ws.xm[rows], geo=geo, bias_scale=n_nbr,
+                         gate=(tab(mod_mva), 2))
+                ops.gemm(ws.xm[rows], self.mva_proj.weight, self.mva_proj.bias, x[rows], geo=geo, res=x[rows])
+
+            ctx.spatial_attention(ops, ws.qkv, ws.ao, d, ctx.kv_map, scale, cv_qkv_rows, cv_proj_rows)
 
         # (g) MLP
         ops.ln_modulate(x, ws.xm, mod, 3, 4, geo)

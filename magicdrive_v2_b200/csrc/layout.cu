@@ -1,5 +1,8 @@
 // layout.cu — patch gather / scatter and the temporal-attention micro-kernel.
+#include <cstdlib>
+
 #include "common.cuh"
+#include "sm100_ptx.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // patchify: one thread per output element (coalesced stores)
@@ -310,11 +313,199 @@ __global__ void __launch_bounds__(256) temporal_attn_vec_kernel(const bf16* __re
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// bf16 production path (T <= 8, D % 8 == 0): shared-memory staged temporal attention.
+// A CTA owns TA_G token columns (β, s).  The T rows q|k|v of a column (3C contiguous bf16 each) arrive by
+// bulk async copies (one elected thread, one mbarrier) — three resident CTAs per SM keep ~140 KB of reads
+// in flight while the others compute — and four short phases run out of shared memory:
+//   A  RoPE (interleaved pairs) on q and k in place, rounded to bf16 like the reference; q also x scale
+//   B  thread = (column, head, t_q): T scores, fp32 softmax, probabilities rounded to bf16 (reference order
+//      of roundings, blocks.py:255-268) and parked in the first bytes of the thread's own q slice
+//   C  thread = (column, head, 8-dim slice): out[t_q] = sum_k P[t_q][k] v[k] for all t_q, written over k
+//   D  bulk async stores of the T output rows
+// Row pitch = 3C·2 + 80 bytes: the 20-word skew makes the (head, t_q) threads of phase B hit eight distinct
+// 16-byte bank groups per quarter warp (bank group = (head + 5·t_q) mod 8 = 5·thread mod 8).
+// The strided gather / scatter never materialises the reference's two transposes (stdit3.py:232-234).
+// ------------------------------------------------------------------------------------------------
+constexpr int TA_G = 2, TA_THREADS = 256, TA_PAD = 80;
+
+template <int TN>
+__global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_kernel(const bf16* __restrict__ qkv, int64_t ld,
+                                                                          const float* __restrict__ cos_t,
+                                                                          const float* __restrict__ sin_t,
+                                                                          bf16* __restrict__ out, int64_t ldo,
+                                                                          int64_t n_cols, int S, int H, int D,
+                                                                          float scale) {
+  using namespace sm100;
+  extern __shared__ __align__(128) uint8_t ta_smem[];
+  const int C = H * D;
+  const int row_bytes = 3 * C * 2, pitch = row_bytes + TA_PAD;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(ta_smem + TA_G * TN * pitch);
+  const int tid = threadIdx.x;
+  const int64_t col0 = (int64_t)blockIdx.x * TA_G;
+  const int ng = (int)((n_cols - col0) < TA_G ? (n_cols - col0) : TA_G);
+  auto grow = [&](int g, int t) {                       // global row of (column col0+g, frame t)
+    const int64_t c = col0 + g, beta = c / S, s = c - beta * S;
+    return (beta * TN + t) * S + s;
+  };
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+    mbar_expect_tx(bar, (uint32_t)(ng * TN * row_bytes));
+    for (int g = 0; g < ng; ++g)
+      for (int t = 0; t < TN; ++t)
+        bulk_g2s(ta_smem + (g * TN + t) * pitch, qkv + grow(g, t) * ld, (uint32_t)row_bytes, bar);
+  }
+  __syncthreads();                                      // barrier init visible to the waiters
+  mbar_wait(bar, 0);
+
+  const int vpr = C / 8;                                // 16-byte vectors per q (or k, v) row part
+  const int vph = D / 8;                                // ... per head
+  // ---- A: RoPE on q and k ----
+  for (int i = tid; i < ng * TN * 2 * vpr; i += TA_THREADS) {
+    const int v = i % vpr, part = (i / vpr) & 1, t = (i / (2 * vpr)) % TN, g = i / (2 * vpr * TN);
+    const int d0 = (v % vph) * 8;
+    uint4* ptr = reinterpret_cast<uint4*>(ta_smem + (g * TN + t) * pitch + part * C * 2 + v * 16);
+    Vec16<bf16> x;
+    x.raw = *ptr;
+    float f[8], o[8];
+    x.unpack(f);
+    const float4 c0 = *reinterpret_cast<const float4*>(cos_t + t * D + d0);
+    const float4 c1 = *reinterpret_cast<const float4*>(cos_t + t * D + d0 + 4);
+    const float4 s0 = *reinterpret_cast<const float4*>(sin_t + t * D + d0);
+    const float4 s1 = *reinterpret_cast<const float4*>(sin_t + t * D + d0 + 4);
+    const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+    const float sn[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+    for (int e = 0; e < 8; e += 2) {
+      o[e] = f[e] * cs[e] - f[e + 1] * sn[e];
+      o[e + 1] = f[e + 1] * cs[e + 1] + f[e] * sn[e + 1];
+    }
+    x.pack(o);
+    if (part == 0) {                                    // q = (rope(q) in bf16) * scale, in bf16
+      x.unpack(f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] *= scale;
+      x.pack(f);
+    }
+    *ptr = x.raw;
+  }
+  __syncthreads();
+  // ---- B: scores + softmax; P[t_q][0..TN) -> first bytes of this thread's q slice ----
+  if (tid < ng * H * TN) {
+    const int tq = tid % TN, h = (tid / TN) % H, g = tid / (TN * H);
+    const uint8_t* qs = ta_smem + (g * TN + tq) * pitch + h * D * 2;
+    float acc[TN];
+#pragma unroll
+    for (int t = 0; t < TN; ++t) acc[t] = 0.f;
+    for (int j = 0; j < vph; ++j) {
+      Vec16<bf16> qv;
+      qv.raw = *reinterpret_cast<const uint4*>(qs + j * 16);
+      float q[8];
+      qv.unpack(q);
+#pragma unroll
+      for (int t = 0; t < TN; ++t) {
+        Vec16<bf16> kv;
+        kv.raw = *reinterpret_cast<const uint4*>(ta_smem + (g * TN + t) * pitch + C * 2 + h * D * 2 + j * 16);
+        float k[8];
+        kv.unpack(k);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[t] += q[e] * k[e];
+      }
+    }
+    float mx = -INFINITY;
+#pragma unroll
+    for (int t = 0; t < TN; ++t) {
+      acc[t] = __bfloat162float(__float2bfloat16_rn(acc[t]));      // q @ k^T leaves the GEMM in bf16
+      mx = fmaxf(mx, acc[t]);
+    }
+    float den = 0.f;
+#pragma unroll
+    for (int t = 0; t < TN; ++t) {
+      acc[t] = __expf(acc[t] - mx);
+      den += acc[t];
+    }
+    const float inv = 1.f / den;
+    float pr[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) pr[t] = t < TN ? __bfloat162float(__float2bfloat16_rn(acc[t] * inv)) : 0.f;
+    float4* pd = reinterpret_cast<float4*>(const_cast<uint8_t*>(qs));
+    pd[0] = make_float4(pr[0], pr[1], pr[2], pr[3]);
+    if (TN > 4) pd[1] = make_float4(pr[4], pr[5], pr[6], pr[7]);
+  }
+  __syncthreads();
+  // ---- C: out[t_q][8 dims] = sum_k P[t_q][k] v[k][8 dims], written over the k part of row t_q ----
+  for (int i = tid; i < ng * H * vph; i += TA_THREADS) {
+    const int j = i % vph, h = (i / vph) % H, g = i / (vph * H);
+    float v[TN][8];
+#pragma unroll
+    for (int t = 0; t < TN; ++t) {
+      Vec16<bf16> vv;
+      vv.raw = *reinterpret_cast<const uint4*>(ta_smem + (g * TN + t) * pitch + 2 * C * 2 + h * D * 2 + j * 16);
+      vv.unpack(v[t]);
+    }
+#pragma unroll
+    for (int tq = 0; tq < TN; ++tq) {
+      const float4* pp = reinterpret_cast<const float4*>(ta_smem + (g * TN + tq) * pitch + h * D * 2);
+      const float4 p0 = pp[0];
+      float pr[8] = {p0.x, p0.y, p0.z, p0.w, 0.f, 0.f, 0.f, 0.f};
+      if (TN > 4) {
+        const float4 p1 = pp[1];
+        pr[4] = p1.x; pr[5] = p1.y; pr[6] = p1.z; pr[7] = p1.w;
+      }
+      float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int t = 0; t < TN; ++t) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] += pr[t] * v[t][e];
+      }
+      Vec16<bf16> ov;
+      ov.pack(o);
+      *reinterpret_cast<uint4*>(ta_smem + (g * TN + tq) * pitch + C * 2 + h * D * 2 + j * 16) = ov.raw;
+    }
+  }
+  fence_async_smem();                                   // generic-proxy writes -> visible to the bulk stores
+  __syncthreads();
+  // ---- D: T output rows per column ----
+  if (tid == 0) {
+    for (int g = 0; g < ng; ++g)
+      for (int t = 0; t < TN; ++t)
+        bulk_s2g(out + grow(g, t) * ldo, ta_smem + (g * TN + t) * pitch + C * 2, (uint32_t)(C * 2));
+    bulk_commit();
+    bulk_wait_read0();                                  // shared memory must outlive the reads
+  }
+}
+
 template <typename T>
 static int launch_temporal(const void* qkv, int64_t ld, const float* c, const float* s, void* out, int64_t ldo,
                            int B, int Tn, int S, int H, int D, float scale, cudaStream_t st) {
   const int64_t n_warps = (int64_t)B * S * H;
   if constexpr (sizeof(T) == 2) {
+    const int C = H * D;
+    const size_t smem = (size_t)TA_G * Tn * (3 * C * 2 + TA_PAD) + 16;
+    static const bool legacy = getenv("MDV2_TEMPORAL_LEGACY") != nullptr;       // tuning hook (tools/bench_elem.py)
+    if (!legacy && Tn <= 8 && D % 8 == 0 && D * 2 >= 32 && ld % 8 == 0 && ldo % 8 == 0 && ((uintptr_t)qkv % 16 == 0) &&
+        ((uintptr_t)out % 16 == 0) && ((uintptr_t)c % 16 == 0) && ((uintptr_t)s % 16 == 0) && smem <= 75 * 1024 &&
+        TA_G * H * Tn <= TA_THREADS) {
+      const int64_t n_cols = (int64_t)B * S;
+      const unsigned nb = (unsigned)((n_cols + TA_G - 1) / TA_G);
+#define TS_CASE(TT)                                                                                               \
+  case TT: {                                                                                                      \
+    static bool configured = false;                                                                               \
+    if (!configured) {                                                                                            \
+      cudaFuncSetAttribute(temporal_attn_smem_kernel<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024); \
+      configured = true;                                                                                          \
+    }                                                                                                             \
+    temporal_attn_smem_kernel<TT><<<nb, TA_THREADS, smem, st>>>((const bf16*)qkv, ld, c, s, (bf16*)out, ldo, n_cols, \
+                                                               S, H, D, scale);                                   \
+  } break
+      switch (Tn) {
+        TS_CASE(1); TS_CASE(2); TS_CASE(3); TS_CASE(4); TS_CASE(5); TS_CASE(6); TS_CASE(7); TS_CASE(8);
+      }
+#undef TS_CASE
+      MDV2_CHECK_LAUNCH("temporal_attention");
+      return MDV2_OK;
+    }
     if (Tn <= 8 && D % 8 == 0 && D <= 128 && ld % 8 == 0 && ldo % 8 == 0 && ((uintptr_t)qkv % 16 == 0) &&
         ((uintptr_t)out % 16 == 0)) {
       const unsigned nb = (unsigned)((n_warps + 15) / 16);
@@ -391,5 +582,77 @@ extern "C" int mdv2_swap01(const void* src, void* dst, int64_t A, int64_t B, int
   swap01_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)src, (uint4*)dst, (uint32_t)A,
                                                                     (uint32_t)B, (uint32_t)inner, total);
   MDV2_CHECK_LAUNCH("swap01");
+  return MDV2_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// scatter_runs: see include/mdv2.h.  One 16-byte vector per thread and grid-stride step; the run index is
+// decomposed with 32-bit divisions (a few ALU ops per 16 bytes against an NVLink- or HBM-bound copy).
+// ------------------------------------------------------------------------------------------------
+struct ScatterArgs {
+  uint4* dst[8];
+  uint32_t size[4];
+  int64_t sstr[4], dstr[4];                            // in 16-byte units
+  int64_t dst_base;
+  uint32_t run;                                        // 16-byte vectors per run
+  int peer_dim;
+};
+
+__global__ void __launch_bounds__(256) scatter_runs_kernel(const uint4* __restrict__ src, const ScatterArgs a,
+                                                           int64_t total) {
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = idx / a.run;
+    const uint32_t v = (uint32_t)(idx - r * a.run);
+    // r = ((i0·size1 + i1)·size2 + i2)·size3 + i3
+    const int64_t r2 = r / a.size[3];
+    const uint32_t i3 = (uint32_t)(r - r2 * a.size[3]);
+    const int64_t r1 = r2 / a.size[2];
+    const uint32_t i2 = (uint32_t)(r2 - r1 * a.size[2]);
+    const uint32_t i0 = (uint32_t)(r1 / a.size[1]);
+    const uint32_t i1 = (uint32_t)(r1 - (int64_t)i0 * a.size[1]);
+    const uint32_t ii[4] = {i0, i1, i2, i3};
+    int64_t so = v, dof = a.dst_base + v;
+    uint32_t peer = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      so += (int64_t)ii[k] * a.sstr[k];
+      if (k == a.peer_dim) peer = ii[k];
+      else dof += (int64_t)ii[k] * a.dstr[k];
+    }
+    a.dst[peer][dof] = src[so];
+  }
+}
+
+extern "C" int mdv2_scatter_runs(const void* src, void* const* dst_ptrs, int n_dst, int peer_dim, const int64_t* sizes,
+                                 const int64_t* src_strides, const int64_t* dst_strides, int64_t run_bytes,
+                                 int64_t dst_base, void* stream) {
+  MDV2_REQUIRE(n_dst >= 1 && n_dst <= 8, "scatter_runs: 1..8 destinations");
+  MDV2_REQUIRE(peer_dim >= 0 && peer_dim < 4 && sizes[peer_dim] == n_dst, "scatter_runs: peer dimension must span the destinations");
+  MDV2_REQUIRE(run_bytes > 0 && run_bytes % 16 == 0 && dst_base % 16 == 0 && ((uintptr_t)src % 16 == 0),
+               "scatter_runs: runs must be 16-byte aligned");
+  ScatterArgs a;
+  int64_t total = run_bytes / 16;
+  for (int k = 0; k < 4; ++k) {
+    MDV2_REQUIRE(sizes[k] >= 1 && sizes[k] < (1ll << 31), "scatter_runs: bad size");
+    MDV2_REQUIRE(src_strides[k] % 16 == 0 && dst_strides[k] % 16 == 0, "scatter_runs: strides must be multiples of 16 bytes");
+    a.size[k] = (uint32_t)sizes[k];
+    a.sstr[k] = src_strides[k] / 16;
+    a.dstr[k] = dst_strides[k] / 16;
+    total *= sizes[k];
+  }
+  for (int i = 0; i < 8; ++i) {
+    a.dst[i] = (uint4*)(i < n_dst ? dst_ptrs[i] : nullptr);
+    MDV2_REQUIRE(i >= n_dst || (dst_ptrs[i] != nullptr && (uintptr_t)dst_ptrs[i] % 16 == 0), "scatter_runs: bad destination");
+  }
+  a.dst_base = dst_base / 16;
+  a.run = (uint32_t)(run_bytes / 16);
+  a.peer_dim = peer_dim;
+  if (total == 0) return MDV2_OK;
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = (int64_t)mdv2_num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  scatter_runs_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)src, a, total);
+  MDV2_CHECK_LAUNCH("scatter_runs");
   return MDV2_OK;
 }

@@ -39,12 +39,14 @@ _lib.mdv2_temporal_attention.argtypes = [_vp, _i64, _vp, _vp, _vp, _i64, _i32, _
 _lib.mdv2_patchify.argtypes = [_vp, _vp] + [_i32] * 11 + [_vp]
 _lib.mdv2_unpatchify.argtypes = [_vp, _vp] + [_i32] * 10 + [_vp]
 _lib.mdv2_swap01.argtypes = [_vp, _vp, _i64, _i64, _i64, _vp]
+_lib.mdv2_scatter_runs.argtypes = [_vp, ctypes.POINTER(_vp), _i32, _i32, ctypes.POINTER(_i64), ctypes.POINTER(_i64),
+                                   ctypes.POINTER(_i64), _i64, _i64, _vp]
 for _f in ("mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention", "mdv2_temporal_attention", "mdv2_patchify",
-           "mdv2_unpatchify", "mdv2_swap01"):
+           "mdv2_unpatchify", "mdv2_swap01", "mdv2_scatter_runs"):
     getattr(_lib, _f).restype = _i32
 
 EXPORTS = ("mdv2_version", "mdv2_last_error", "mdv2_last_kernel", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention",
-           "mdv2_temporal_attention", "mdv2_patchify", "mdv2_unpatchify", "mdv2_swap01")
+           "mdv2_temporal_attention", "mdv2_patchify", "mdv2_unpatchify", "mdv2_swap01", "mdv2_scatter_runs")
 
 # kernel-launch counter (bench.py reports it as gpu_launches); +1 per C-ABI call that launches
 launches = 0
@@ -241,3 +243,21 @@ def swap01(src, dst, A, B, inner):
     _check(_lib.mdv2_swap01(_ptr(src), _ptr(dst), A, B, inner * src.element_size(), _stream()), "mdv2_swap01")
     _t1(e0, "", 0, 2 * src.numel() * src.element_size())
     return dst
+
+
+def scatter_runs(src, dst_ptrs, peer_dim, sizes, src_strides, dst_strides, run, dst_base=0):
+    """Strided scatter of contiguous runs of ``run`` elements of ``src`` into the buffers ``dst_ptrs`` (raw device
+    addresses, e.g. the NVLink-mapped peers of a symmetric allocation); index ``peer_dim`` selects the destination.
+    Strides, ``run`` and ``dst_base`` are in elements of ``src``'s dtype."""
+    es = src.element_size()
+    n = len(dst_ptrs)
+    arr = (_vp * n)(*[_vp(int(q)) for q in dst_ptrs])
+    I4 = _i64 * 4
+    e0 = _t0()
+    _check(_lib.mdv2_scatter_runs(_ptr(src), arr, n, peer_dim, I4(*sizes), I4(*[x * es for x in src_strides]),
+                                  I4(*[x * es for x in dst_strides]), run * es, dst_base * es, _stream()),
+           "mdv2_scatter_runs")
+    nb = run * es
+    for x in sizes:
+        nb *= x
+    _t1(e0, "", 0, 2 * nb)

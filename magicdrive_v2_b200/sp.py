@@ -84,13 +84,20 @@ def _buf(tag, shape, like):
     return t
 
 
-def ulysses_attention(ops, qkv, out, d, kv_map, scale, group, p):
+def ulysses_attention(ops, qkv, out, d, kv_map, scale, group, p, produce, consume):
     """Spatial / cross-view attention under sequence parallelism (blocks.py:546-645, without its copies).
 
     qkv: [N_l, 3C] local tokens (rows (β, t, s_l)), columns q|k|v with heads in rank order; out: [N_l, C].
-    The work is split into the b scheduler-batch halves (each closed under the cross-view neighbour map), and
-    the chunks are software-pipelined: while chunk c runs attention, the NCCL stream moves chunk c+1's q/k/v
-    and chunk c-1's output.  Every re-ordering is one `swap01` launch at HBM speed:
+    ``produce(rows, tab)`` computes ``qkv[rows]`` and ``consume(rows, tab)`` folds ``out[rows]`` into the
+    residual stream (the projections around the attention, see MagicDriveSTDiT3._spatial_attention).
+
+    The work is split into the b scheduler-batch halves (each closed under the cross-view neighbour map) and
+    software-pipelined over them, with NCCL running on its own stream:
+
+        produce(0) | produce(1) ‖ a2a(0) | attn(0) ‖ a2a(1) | attn(1) ‖ a2a'(0) | consume(0) ‖ a2a'(1) | consume(1)
+
+    so every all-to-all has a GEMM or an attention of the other half to hide behind.  Every re-ordering is one
+    `swap01` launch at HBM speed:
 
         qkv [n·3][p][HpD]        -> send  [p][n·3][HpD]          heads scatter   (then all-to-all)
         recv [p][β'·T][Sl·3·HpD] -> full  [β'·T][p·Sl][3][HpD]   sequence gather
@@ -101,7 +108,8 @@ def ulysses_attention(ops, qkv, out, d, kv_map, scale, group, p):
     Hp = H // p
     HpD = Hp * D
     n_chunks = d.b if d.b > 1 else 1
-    BTc = d.NC * d.T * (d.b // n_chunks)                 # sequences per chunk
+    bc = d.b // n_chunks                                 # scheduler-batch entries per chunk
+    BTc = d.NC * d.T * bc                                # sequences per chunk
     Nc = BTc * Sl                                        # local tokens per chunk
     assert qkv.is_contiguous() and out.is_contiguous() and qkv.shape == (d.N, 3 * C)
     maps = [None] * n_chunks
@@ -109,12 +117,20 @@ def ulysses_attention(ops, qkv, out, d, kv_map, scale, group, p):
         for c in range(n_chunks):
             m = kv_map[c * BTc:(c + 1) * BTc] - c * BTc
             maps[c] = m.contiguous()
+
+    def rows_of(c):
+        return slice(c * Nc, (c + 1) * Nc)
+
+    def tab_of(c):                                       # modulation tables are [b·T, K, C]
+        return lambda m: m[c * bc * d.T:(c + 1) * bc * d.T]
+
     work1, work2 = [None] * n_chunks, [None] * n_chunks
     recv, recv2 = [None] * n_chunks, [None] * n_chunks
     for c in range(n_chunks):
+        produce(rows_of(c), tab_of(c))
         send = _buf(("send", c), (p, Nc * 3, HpD), qkv)
         recv[c] = _buf(("recv", c), (p, Nc * 3, HpD), qkv)
-        ops.swap01(qkv[c * Nc:(c + 1) * Nc], send, Nc * 3, p, HpD)
+        ops.swap01(qkv[rows_of(c)], send, Nc * 3, p, HpD)
         work1[c] = dist.all_to_all_single(recv[c], send, group=group, async_op=True)
     for c in range(n_chunks):
         full = _buf(("full", c), (BTc * p * Sl, 3 * HpD), qkv)
@@ -129,7 +145,82 @@ def ulysses_attention(ops, qkv, out, d, kv_map, scale, group, p):
         work2[c] = dist.all_to_all_single(recv2[c], send2, group=group, async_op=True)
     for c in range(n_chunks):
         work2[c].wait()
-        ops.swap01(recv2[c], out[c * Nc:(c + 1) * Nc], p, Nc, HpD)
+        ops.swap01(recv2[c], out[rows_of(c)], p, Nc, HpD)
+        consume(rows_of(c), tab_of(c))
+
+
+# ---------------------------------------------------------------------------------------------------
+# NVLink peer-memory exchange (one process per GPU of one NVSwitch box): the re-sharding all-to-alls become
+# ONE libmdv2 scatter kernel each, storing straight into the final layout in the peers' HBM.
+# ---------------------------------------------------------------------------------------------------
+_SYMM = {}
+_SYMM_OK = None
+
+
+def peer_exchange_available(like: torch.Tensor, group) -> bool:
+    """True when the ranks of ``group`` can map each other's device memory (torch symmetric memory over CUDA
+    IPC / NVLink) and there are at most 8 of them.  ``MDV2_SP_NCCL=1`` forces the NCCL all-to-all path."""
+    global _SYMM_OK
+    import os
+    if not like.is_cuda or os.environ.get("MDV2_SP_NCCL") or dist.get_world_size(group) > 8:
+        return False
+    if _SYMM_OK is None:
+        try:
+            import torch.distributed._symmetric_memory as symm
+            t = symm.empty(1024, dtype=torch.uint8, device=like.device)
+            symm.rendezvous(t, group.group_name)
+            _SYMM_OK = True
+        except Exception:                                 # noqa: BLE001 - any failure means "not available here"
+            _SYMM_OK = False
+        flag = torch.tensor([1 if _SYMM_OK else 0], device=like.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)      # all ranks take the same path
+        _SYMM_OK = bool(flag.item())
+    return _SYMM_OK
+
+
+def symm_buffer(tag, shape, like, group):
+    """-> (tensor, handle, peer base addresses): a symmetric allocation per (tag, shape), made collectively."""
+    import torch.distributed._symmetric_memory as symm
+    key = (tag, tuple(shape), like.dtype, like.device, group.group_name)
+    ent = _SYMM.get(key)
+    if ent is None:
+        t = symm.empty(tuple(shape), dtype=like.dtype, device=like.device)
+        hdl = symm.rendezvous(t, group.group_name)
+        ent = _SYMM[key] = (t, hdl, [int(a) for a in hdl.buffer_ptrs])
+    return ent
+
+
+def ulysses_attention_peer(ops, qkv, ao_sym, d, kv_map, scale, group, p, rank, produce, consume):
+    """Same contract as ``ulysses_attention`` over peer memory.  ``ao_sym = (tensor, handle, peer addresses)`` is
+    the symmetric buffer that ``consume`` reads the attention output from (the workspace's ``ao``).
+
+        produce -> scatter(q|k|v heads -> owner ranks, straight into [β·T, S, 3, Hp·D]) -> barrier -> attention
+                -> scatter(output rows -> owner ranks, straight into their [N_l, C]) -> barrier -> consume
+
+    No pack / unpack copies and no NCCL call: the scatter kernel reads local HBM once and writes the peers'
+    HBM through NVLink.  The only cross-rank ordering is the barrier behind each scatter; a buffer is next
+    overwritten only after a later barrier that every rank reaches after it has finished reading it."""
+    Sl, H, D, C = d.S, d.H, d.D, d.C
+    Hp = H // p
+    HpD = Hp * D
+    BT = d.B * d.T
+    rows = slice(0, d.N)
+    ident = lambda m: m                                   # noqa: E731
+    produce(rows, ident)
+    full, hdl_f, ptrs_f = symm_buffer("full", (BT * p * Sl, 3 * HpD), qkv, group)
+    # index order (β·t, s, rank, q|k|v): the three runs of one (token, rank) land back to back in the peer's row, so
+    # consecutive threads write 3·Hp·D contiguous elements over NVLink
+    ops.scatter_runs(qkv, ptrs_f, 2, (BT, Sl, p, 3), (Sl * 3 * C, 3 * C, HpD, C),
+                     (p * Sl * 3 * HpD, 3 * HpD, 0, HpD), HpD, dst_base=rank * Sl * 3 * HpD)
+    hdl_f.barrier()
+    o = _buf(("o", 0), (BT * p * Sl, HpD), qkv)
+    ops.attention(full[:, :HpD], full[:, HpD:2 * HpD], full[:, 2 * HpD:], o, BT, p * Sl, p * Sl, Hp, D, scale,
+                  kv_map=kv_map)
+    ao, hdl_a, ptrs_a = ao_sym
+    ops.scatter_runs(o, ptrs_a, 1, (BT, p, Sl, 1), (p * Sl * HpD, Sl * HpD, HpD, 0), (Sl * C, 0, C, 0), HpD,
+                     dst_base=rank * HpD)
+    hdl_a.barrier()
+    consume(rows, ident)
 
 
 def gather_tokens(yo, d, p, group):

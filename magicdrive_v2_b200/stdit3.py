@@ -435,6 +435,12 @@ class MagicDriveSTDiT3(PreTrainedModel):
         d = Dims(b=b, NC=NC, T=T, S=Sl, C=C, H=NH, D=C // NH)
         if self._ws is None or self._ws.key != (d.N, C, dtype, dev, self.mlp_ratio):
             self._ws = Workspace(d, dtype, dev, self.mlp_ratio)
+            self._ws.ao_sym = None
+            from . import sp
+            if p > 1 and sp.peer_exchange_available(x, sp_group):
+                # the attention output buffer is written by the peers (NVLink scatter): symmetric allocation
+                self._ws.ao_sym = sp.symm_buffer("ao", (d.N, C), self._ws.ao, sp_group)
+                self._ws.ao = self._ws.ao_sym[0]
         ws = self._ws
         N = d.N
         patches = torch.empty(N, self.in_channels * 4, dtype=dtype, device=dev)
@@ -516,17 +522,29 @@ class MagicDriveSTDiT3(PreTrainedModel):
         group = self.sp_group if self.sp_group is not None else sp.get_sequence_parallel_group()
         return group, torch.distributed.get_world_size(group), torch.distributed.get_rank(group)
 
-    def _spatial_attention(self, ops, qkv, out, d: Dims, kv_map, scale):
+    def _spatial_attention(self, ops, qkv, out, d: Dims, kv_map, scale, produce, consume):
         """Attention over the S tokens of every (β, t) frame (qkv: [N, 3C], columns q|k|v); with kv_map
-        the K/V come from the neighbour views and the per-neighbour results are summed (cross-view, P5)."""
+        the K/V come from the neighbour views and the per-neighbour results are summed (cross-view, P5).
+
+        ``produce(rows, tab)`` fills ``qkv[rows]`` (LN-modulate + qkv projection) and ``consume(rows, tab)``
+        folds ``out[rows]`` back into the residual stream (output projection); ``tab(mod)`` narrows a
+        modulation table to the scheduler-batch entries of those rows.  On one GPU both run once over all
+        rows; under sequence parallelism they run per chunk so the all-to-alls hide behind them."""
         group, p, _ = self._sp()
         if p == 1:
             C = d.C
+            rows = slice(0, d.N)
+            produce(rows, lambda m: m)
             ops.attention(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], out, d.B * d.T, d.S, d.S, d.H, d.D, scale,
                           kv_map=kv_map)
+            consume(rows, lambda m: m)
             return
         from . import sp
-        sp.ulysses_attention(ops, qkv, out, d, kv_map, scale, group, p)
+        if self._ws is not None and getattr(self._ws, "ao_sym", None) is not None:
+            _, _, rank = self._sp()
+            sp.ulysses_attention_peer(ops, qkv, self._ws.ao_sym, d, kv_map, scale, group, p, rank, produce, consume)
+            return
+        sp.ulysses_attention(ops, qkv, out, d, kv_map, scale, group, p, produce, consume)
 
     def _sp_gather_tokens(self, yo, d: Dims, p, group):
         from . import sp

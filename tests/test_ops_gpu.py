@@ -247,3 +247,33 @@ def test_swap01_bit_exact(dtype):
         ops().swap01(src, dst, A, B, inner)
         spec_ops.swap01(src, ref, A, B, inner)
         assert torch.equal(dst, ref)
+
+
+def test_scatter_runs_matches_all_to_all_layouts():
+    """The two Ulysses re-shardings expressed as scatter_runs, with all "ranks" living on one GPU: the result must
+    equal the reference's split / all_to_all / rearrange chain (communications.py:11-66, blocks.py:571-638)."""
+    bf = torch.bfloat16
+    p, BT, Sl, Hp, D = 4, 3, 5, 2, 72
+    HpD, C = Hp * D, p * Hp * D
+    # exchange 1: qkv_r [BT·Sl, 3C] on every rank r  ->  full_q [BT, p·Sl, 3, HpD] on every rank q
+    qkv = [rnd(BT * Sl, 3 * C, dtype=bf, seed=10 + r) for r in range(p)]
+    full = [torch.zeros(BT * p * Sl, 3 * HpD, dtype=bf, device=DEV) for _ in range(p)]
+    ptrs = [t.data_ptr() for t in full]
+    for r in range(p):
+        ops().scatter_runs(qkv[r], ptrs, 2, (BT, Sl, p, 3), (Sl * 3 * C, 3 * C, HpD, C),
+                           (p * Sl * 3 * HpD, 3 * HpD, 0, HpD), HpD, dst_base=r * Sl * 3 * HpD)
+    torch.cuda.synchronize()
+    for q in range(p):
+        ref = torch.stack([qkv[r].view(BT, Sl, 3, p, HpD)[:, :, :, q] for r in range(p)], dim=1)   # [BT, p, Sl, 3, HpD]
+        assert torch.equal(full[q].view(BT, p, Sl, 3, HpD), ref)
+    # exchange 2: o_q [BT, p·Sl, HpD] on every rank q  ->  ao_r [BT·Sl, C] on every rank r
+    o = [rnd(BT * p * Sl, HpD, dtype=bf, seed=30 + q) for q in range(p)]
+    ao = [torch.zeros(BT * Sl, C, dtype=bf, device=DEV) for _ in range(p)]
+    ptrs = [t.data_ptr() for t in ao]
+    for q in range(p):
+        ops().scatter_runs(o[q], ptrs, 1, (BT, p, Sl, 1), (p * Sl * HpD, Sl * HpD, HpD, 0), (Sl * C, 0, C, 0), HpD,
+                           dst_base=q * HpD)
+    torch.cuda.synchronize()
+    for r in range(p):
+        ref = torch.stack([o[q].view(BT, p, Sl, HpD)[:, r] for q in range(p)], dim=2)               # [BT, Sl, p, HpD]
+        assert torch.equal(ao[r].view(BT, Sl, p, HpD), ref)

@@ -19,7 +19,7 @@ def _free_port():
     return port
 
 
-def _worker(rank, world, port, wl_name, xm, ret):
+def _worker(rank, world, port, wl_name, xm, ret, nccl_path):
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     for p in (root, os.path.join(root, "tests")):
@@ -29,6 +29,10 @@ def _worker(rank, world, port, wl_name, xm, ret):
     from magicdrive_v2_b200 import sp, synth
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
+    if nccl_path:
+        os.environ["MDV2_SP_NCCL"] = "1"                 # NCCL all-to-all instead of the NVLink peer scatter
+    else:
+        os.environ.pop("MDV2_SP_NCCL", None)
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
@@ -40,19 +44,23 @@ def _worker(rank, world, port, wl_name, xm, ret):
             model = model.to(dev, dtype)
             inp = synth.to_device(synth.make_inputs(wl, seed=fix["seed"], x_mask=xm, kw=kw), dev)
             out = model(**inp)
+            out = model(**inp)                            # second call: peer buffers are reused across forwards
             torch.cuda.synchronize()
             ret[(rank, key)] = rel_l2(out.cpu(), fix["out"])
+            ret[(rank, "peer")] = getattr(model._ws, "ao_sym", None) is not None
     finally:
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("nccl_path", [False, True])
 @pytest.mark.parametrize("wl_name,xm", [("tiny_d72", "first0")])
-def test_sequence_parallel_nccl_world2(wl_name, xm):
+def test_sequence_parallel_nccl_world2(wl_name, xm, nccl_path):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     world = 2
     ret = mp.Manager().dict()
-    mp.spawn(_worker, args=(world, _free_port(), wl_name, xm, ret), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), wl_name, xm, ret, nccl_path), nprocs=world, join=True)
     for r in range(world):
+        assert ret[(r, "peer")] == (not nccl_path), "wrong exchange path taken"
         assert ret[(r, "fp32")] < 1e-4, ret[(r, "fp32")]
         assert ret[(r, "bf16")] < 1e-2, ret[(r, "bf16")]
