@@ -391,6 +391,16 @@ def main():
                     peak_source=pk["source"] + (", sustained bf16 (kernel timed inside a long step)"
                                                 if drow["bound"] == "tensor" else ", copy bandwidth"),
                     how="CUDA-event pair around every libmdv2 call of one instrumented step, summed per kernel")
+    # DRAM traffic of one representative launch per kernel family, from the committed `ncu --set full` captures
+    # (dram__bytes_read.sum + dram__bytes_write.sum; profiles/ncu_traffic_r01.json names launch and capture file)
+    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic_r01.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            ttab = json.load(f)
+        for fam, row in ktab.items():
+            if fam in ttab:
+                row["traffic"] = ttab[fam]
+        roofline["traffic"] = ttab.get(dom)
     step_tf = fl["total"] / world / (res["ms_step"] * 1e-3) / 1e12
     line = dict(metric=METRIC, value=1e3 / res["ms_step"], unit=UNIT, n_gpus=world, steps=args.steps,
                 warmup=args.warmup, ms_per_step=res["ms_step"], higher_is_better=True, scaling="strong",

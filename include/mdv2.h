@@ -99,6 +99,17 @@ int mdv2_scatter_runs(const void* src, void* const* dst_ptrs, int n_dst, int pee
                       const int64_t* src_strides, const int64_t* dst_strides, int64_t run_bytes, int64_t dst_base,
                       void* stream);
 
+/* Tail of one RFLOW sampling step (magicdrivedit/schedulers/rf/__init__.py:100-109) plus the head of the next
+ * (:95 and the x.to(dtype) of magicdrive_stdit3.py:1041), fused into one pass:
+ *   v = pred[n:] + guidance * (pred[:n] - pred[n:]);  z_out = z + v * dt[b]        (fp32, each op rounded separately)
+ *   if keep: z_out = keep[b, t] ? z_out : x0           (frame mask `mask_t_upper` [n, T] as bytes; x0 has z's dtype)
+ *   if z_in:  z_in[0:n] = z_in[n:2n] = cast(z_out)     (zin_dtype 0 = fp32, 1 = bf16: the next forward's input)
+ * pred is the model's fp32 output [2n, C, T, hw]; z is [n, C, T, hw] of z_dtype (0 fp32, 1 bf16); dt is a device
+ * vector of n floats (already divided by num_timesteps).  z_out may alias z when z is fp32. */
+int mdv2_cfg_euler_step(const float* pred, const void* z, int z_dtype, const float* dt, float guidance,
+                        const void* x0, const uint8_t* keep, float* z_out, void* z_in, int zin_dtype, int n, int C,
+                        int T, int64_t hw, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

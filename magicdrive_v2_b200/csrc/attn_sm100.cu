@@ -32,10 +32,22 @@ int mdv2_make_tmap_3d_heads(CUtensorMap* out, const void* ptr, uint64_t rows, ui
 
 namespace {
 constexpr int BMQ = 128;          // query rows per tile
-constexpr int NTHREADS = 352;    // TMA, MMA(tile 0), 8 softmax warps, MMA(tile 1)
-constexpr int TMEM_COLS = 512;
-constexpr int O_COL0 = 256;       // O_t at columns 256 + 128·t ; S_t (and P_t over it) at 128·t
-constexpr int Q_COL0 = 336;       // Q_t (bf16 pairs, DP/2 <= 40 columns) at 336 + 128·t, in the gaps behind O_t
+// CTA shape.  128-key tiles (self / cross-view attention): two query tiles per CTA, 11 warps (TMA, MMA of tile 0,
+// 8 softmax warps, MMA of tile 1), all 512 TMEM columns: S_t (and P_t over it) at 128·t, O_t at 256 + 128·t,
+// Q_t (bf16 pairs, DP/2 <= 40 columns) at 336 + 128·t in the gaps behind O_t.
+// 64-key tiles (cross-attention onto <= 64 condition tokens, a single K/V tile): the CTA is one latency chain
+// (load, one Q·K^T, one softmax, one P·V, store), so it takes ONE query tile, 6 warps, 256 TMEM columns
+// (S at 0, O at 64, Q at 144) and 96 KB of shared memory — two CTAs per SM overlap each other's chain.
+template <int BNK>
+struct AShape {
+  static constexpr int QT = BNK == 64 ? 1 : 2;                       // query tiles per CTA
+  static constexpr int NTHREADS = QT == 2 ? 352 : 192;
+  static constexpr int TMEM_COLS = QT == 2 ? 512 : 256;
+  static constexpr int CTAS_PER_SM = QT == 2 ? 1 : 2;
+  __host__ __device__ static constexpr int s_col(int t) { return QT == 2 ? t * 128 : 0; }
+  __host__ __device__ static constexpr int o_col(int t) { return QT == 2 ? 256 + t * 128 : 64; }
+  __host__ __device__ static constexpr int q_col(int t) { return QT == 2 ? 336 + t * 128 : 144; }
+};
 constexpr float RESCALE_LOG2 = 8.f;
 constexpr int ATTN_PF_DEFAULT = 2;   // polynomial 2^x pairs per 8 pairs (0, 2, 3, 4)
 
@@ -48,7 +60,7 @@ struct ACfg {
   // tiles are recycled as the third K / V stage; the 64-key flavour (single K/V tile) keeps Q apart.
   static constexpr bool ALIAS_Q = BNK == 128;
   static constexpr int KV_STAGES = ALIAS_Q ? 3 : 2;
-  static constexpr int SMEM = KV_STAGES * 2 * KV_BYTES + (ALIAS_Q ? 0 : 2 * Q_BYTES) + 256 + 1024;
+  static constexpr int SMEM = KV_STAGES * 2 * KV_BYTES + (ALIAS_Q ? 0 : AShape<BNK>::QT * Q_BYTES) + 320 + 1024;
   static_assert(!ALIAS_Q || Q_BYTES == KV_BYTES, "Q tile must fit a K/V stage");
 };
 
@@ -59,7 +71,7 @@ struct AParams {
   float scale_log2;
   const int32_t* kv_map;
   long long* trace;        // debug timeline (tools/attn_trace.py) or nullptr
-  int dbg;                 // debug switches (MDV2_ATTN_DBG): bit 0 swaps the TMA / MMA warps
+  int dbg;                 // debug switches (MDV2_ATTN_DBG): bit 0 swaps the TMA / MMA warps, bit 1 disables the ping-pong
 };
 
 constexpr int TRACE_STEPS = 96, TRACE_EV = 12;
@@ -93,14 +105,28 @@ __device__ __forceinline__ float2 ex2_poly2(float2 x) {
   r.y = __uint_as_float(__float_as_uint(q.y) + (__float_as_uint(t.y) << 23));
   return r;
 }
+// Measured (tools/probes/pipe_probe.cu, clk per warp instruction and SM sub-partition): MUFU.EX2 8, FFMA2 3, FADD2 /
+// FMNMX3 / F2FP 2, FFMA / FADD 1.  The packed forms cost pipe time but save issue slots, and the loop below is
+// bound by the MUFU pipe (64 exponentials x 2 resident warps x 8 clk ~ the 1000 clk a half-step takes): a scalar
+// rewrite of the loop was 3 % slower, and moving 1/8..1/2 of the exponentials to this polynomial is neutral to
+// slightly negative at D = 72 (sweep in profiles/), because the issue port then becomes the limit.
+// What bounds the kernel (profiles/attn_trace_r01.txt): a softmax warp's half-step is ONE serial chain — wait S 150,
+// tcgen05.ld 100, ~14 clk of issue per score (the pipe costs above add up within a warp) x 64, tcgen05.st 100 — of
+// ~1400 clk, and only two such chains fit an SM sub-partition (TMEM holds two 128-row tiles).  Tried and measured:
+// ping-pong turns between the two tiles (kept, +4 %: one tile's MMAs run under the other's exponentials); splitting a
+// row over two warps (16 softmax warps at 96 registers, row statistics exchanged through shared memory + a named
+// barrier per half-step): each chain got 30 % shorter but paid 140 clk of exchange, 725 vs 747 TF/s, removed
+// (profiles/attn_trace_rowsplit_r01.txt).
 // pair index (0..BNK/2) -> evaluated by the polynomial?  PF of every 8 pairs, spread evenly.
 __host__ __device__ constexpr bool poly_pair(int pair, int PF) { return ((pair % 8) * PF) / 8 != (((pair % 8) + 1) * PF) / 8; }
 
 template <int DP, int BNK, int PF = 0, bool TRACE = false>
-__global__ void __launch_bounds__(NTHREADS, 1)
+__global__ void __launch_bounds__(AShape<BNK>::NTHREADS, AShape<BNK>::CTAS_PER_SM)
 attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
                   const __grid_constant__ CUtensorMap tv, const AParams p) {
   using C = ACfg<DP, BNK>;
+  using SH = AShape<BNK>;
+  constexpr int QT = SH::QT, TMEM_COLS = SH::TMEM_COLS;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr int KV_STAGES = C::KV_STAGES;
@@ -110,7 +136,7 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
   // Q tile t: over the last K (t = 0) / V (t = 1) stage when aliased, else behind the rings
   uint8_t* sQ0 = C::ALIAS_Q ? sK + (KV_STAGES - 1) * C::KV_BYTES : s_end;
   uint8_t* sQ1 = C::ALIAS_Q ? sV + (KV_STAGES - 1) * C::KV_BYTES : s_end + C::Q_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(C::ALIAS_Q ? s_end : s_end + 2 * C::Q_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(C::ALIAS_Q ? s_end : s_end + QT * C::Q_BYTES);
   uint64_t* q_full = bars;                              // 1
   uint64_t* k_full = bars + 1;                          // KV_STAGES
   uint64_t* k_empty = k_full + KV_STAGES;
@@ -121,6 +147,9 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
   uint64_t* o_full = p_full + 4;                        // [query tile][key half]: P·V of that half-step has completed
   uint64_t* qt_full = o_full + 4;                       // [query tile]: Q_t copied from shared memory into TMEM
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(qt_full + 2);
+  float* pp_zero = reinterpret_cast<float*>(tmem_slot + 1);   // ping-pong turn: a 0.0f read behind the barrier ...
+  float* pp_sink = pp_zero + 1;                               // ... and one word per warp written ahead of the arrive
+  constexpr int mma1_warp = 10;                              // MMA issuer of query tile 1
   constexpr int HB = 64;                                // keys per half-step (S columns handed over at a time)
   constexpr int NH = BNK / HB;                          // half-steps per K/V tile
 
@@ -129,8 +158,8 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
   const int qp = blockIdx.x, h = blockIdx.y, seq = blockIdx.z;
   const int n_kt = (p.Lk + BNK - 1) / BNK;
   const int n_tiles = n_kt * p.n_sets;
-  const int q_row0 = qp * 2 * BMQ;                      // first query row of this CTA within the sequence
-  const int n_qt = (q_row0 + BMQ < p.Lq) ? 2 : 1;       // the second tile may lie entirely past Lq
+  const int q_row0 = qp * QT * BMQ;                     // first query row of this CTA within the sequence
+  const int n_qt = (QT == 2 && q_row0 + BMQ < p.Lq) ? 2 : 1;   // the second tile may lie entirely past Lq
   // debug timeline of one CTA of a middle wave: trace[warp][step][event] = clock64
   const bool tracing = TRACE && p.trace != nullptr && qp == 3 && h == 1 && seq == (int)gridDim.z / 2;
   auto mark = [&](int j, int ev) {
@@ -146,7 +175,7 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     mbar_init(q_full, 1);
     for (int i = 0; i < KV_STAGES; ++i) {
       mbar_init(&k_full[i], 1);
-      mbar_init(&k_empty[i], n_qt);                     // one commit per MMA issuer
+      mbar_init(&k_empty[i], n_qt);                     // one arrival per query tile (its softmax warp 0)
       mbar_init(&v_full[i], 1);
       mbar_init(&v_empty[i], n_qt);
     }
@@ -159,6 +188,7 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     fence_mbar_init();
   }
   if (warp == mma_warp) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (threadIdx.x == 64) *pp_zero = 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -195,7 +225,7 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
         }
       }
     }
-  } else if (warp == 1 || warp == 10) {
+  } else if (warp == 1 || (QT == 2 && warp == mma1_warp)) {
     // ================= MMA issuers: warp 1 -> query tile 0, warp 10 -> query tile 1 =================
     // The whole warp runs the warp-uniform control flow and one elected lane issues each tcgen05 instruction
     // (descriptors live in uniform registers; every shared-memory descriptor is base + constant, the 14-bit
@@ -209,25 +239,28 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
       constexpr uint32_t idesc_pv = make_idesc_bf16(BMQ, DP, 0, 1);     // A = P from TMEM, B = V is MN-major
       const uint64_t dk0 = make_desc_k_sw128(smem_u32(sK));
       const uint64_t dv0 = make_desc_mn_sw128(smem_u32(sV), BNK * 128, 1024);
-      const uint32_t s_tm = tmem_base + t * 128, o_tm = tmem_base + O_COL0 + t * 128, q_tm = tmem_base + Q_COL0 + t * 128;
+      const uint32_t s_tm = tmem_base + SH::s_col(t), o_tm = tmem_base + SH::o_col(t), q_tm = tmem_base + SH::q_col(t);
       // S_t^hf(j) = Q_t · K_j[hf·64 .. hf·64+63]^T  ->  TMEM columns t·128 + hf·64 .. +63.  A = Q_t from TMEM: an SS
       // MMA would re-read the 4 KB Q slice from shared memory for every 64-key half and run at the 128 B/clk
       // shared-memory limit (58 clk per 128x64x16 MMA measured, 32 clk of math)
+      // (called by ONE lane: the MMAs of a half-step are issued back to back from a single elected region — with an
+      // election per instruction the issuer spent ~16 instructions per MMA, and on a sub-partition it shares with
+      // busy softmax warps that, not the tensor pipe, set the pace of the chain)
       auto issue_qk = [&](int hf, int st) {
         const uint64_t db = dk0 + (uint64_t)(st * (C::KV_BYTES >> 4) + hf * ((HB * 128) >> 4));
 #pragma unroll
         for (int ks = 0; ks < DP / 16; ++ks) {
           const uint64_t ob = (uint64_t)((ks / 4) * ((BNK * 128) >> 4) + (ks % 4) * 2);
-          if (elect_one()) umma_bf16_ts(s_tm + hf * HB, q_tm + ks * 8, db + ob, idesc_qk, ks != 0);
+          umma_bf16_ts(s_tm + hf * HB, q_tm + ks * 8, db + ob, idesc_qk, ks != 0);
         }
-        if (elect_one()) umma_commit(&s_full[t * 2 + hf]);
-        __syncwarp();
+        umma_commit(&s_full[t * 2 + hf]);
       };
       mbar_wait(&qt_full[t], 0);
       mbar_wait(&k_full[0], 0);
       tc_fence_after();
-      for (int hf = 0; hf < NH; ++hf) issue_qk(hf, 0);
-      if (elect_one()) umma_commit(&k_empty[0]);
+      if (elect_one()) {
+        for (int hf = 0; hf < NH; ++hf) issue_qk(hf, 0);
+      }
       __syncwarp();
       for (int j = 0; j < n_tiles; ++j) {
         const int st = j % KV_STAGES, st1 = (j + 1) % KV_STAGES;
@@ -243,41 +276,37 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
           tc_fence_after();
           mark(j, 1 + 2 * hf);
           // O_t += P_t^hf · V_j[hf·64 ..]: P^hf sits on the first 32 columns of S_t^hf
+          if (elect_one()) {
 #pragma unroll
-          for (int ks = 0; ks < HB / 16; ++ks)
-            if (elect_one())
+            for (int ks = 0; ks < HB / 16; ++ks)
               umma_bf16_ts(o_tm, s_tm + hf * HB + ks * 8, dv + (uint64_t)((hf * HB + ks * 16) * 128 >> 4), idesc_pv,
                            (ks != 0) || (hf != 0) || !fresh);
-          // O is only read back at the end of a K/V set; in between, "P·V of a half-step has completed" is implied by
-          // the completion of the Q·K^T issued behind it (s_full), so the extra commit (~100 clk of this warp's
-          // issue chain each) is only spent on the last tile of a set
-          if (last_of_set) {
-            if (elect_one()) umma_commit(&o_full[t * 2 + hf]);
-            __syncwarp();
+            // O is only read back at the end of a K/V set; in between, "P·V of a half-step has completed" is implied
+            // by the completion of the Q·K^T issued behind it (s_full), so the extra commit (~100 clk of this warp's
+            // issue chain each) is only spent on the last tile of a set
+            if (last_of_set) umma_commit(&o_full[t * 2 + hf]);
+            if (more) issue_qk(hf, st1);                 // S_t^hf(j+1) over the P it just consumed (in-order pipe)
           }
-          if (more) issue_qk(hf, st1);                   // S_t^hf(j+1) over the P it just consumed (in-order pipe)
+          __syncwarp();
           mark(j, 2 + 2 * hf);
         }
-        if (elect_one()) {
-          umma_commit(&v_empty[st]);
-          if (more) umma_commit(&k_empty[st1]);
-        }
-        __syncwarp();
+        // K_{j+1} and V_j are handed back to the TMA producer by the softmax warps (see there): a tcgen05.commit
+        // costs this warp's issue chain ~100 clk, an mbarrier.arrive from a warp that already knows costs nothing
       }
     }
-  } else if (warp < 10 && ((warp - 2) >> 2) < n_qt) {
+  } else if (warp < 2 + 4 * QT && ((warp - 2) >> 2) < n_qt) {
     // ================= softmax warps: thread = query row =================
     const int t = (warp - 2) >> 2;
     const int quarter = warp & 3;                      // TMEM lane quarter this warp may touch
     const int row = quarter * 32 + lane;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    const uint32_t s_addr = lane_addr + t * 128, o_addr = lane_addr + O_COL0 + t * 128;
+    const uint32_t s_addr = lane_addr + SH::s_col(t), o_addr = lane_addr + SH::o_col(t);
     const int q_idx = q_row0 + t * BMQ + row;
     const float c = p.scale_log2;
     bf16* orow = p.out + ((int64_t)seq * p.Lq + q_idx) * p.ldo + (int64_t)h * p.D;
     {
       // Q_t: this thread's row from the 128-byte-swizzled TMA tile (16-byte unit u of row r sits at u ^ (r % 8))
-      // -> TMEM columns Q_COL0 + 128·t .. (+ DP/2), the A-operand layout (lane = row, bf16 pairs along K)
+      // -> TMEM columns q_col(t) .. (+ DP/2), the A-operand layout (lane = row, bf16 pairs along K)
       mbar_wait(q_full, 0);
       uint32_t qw[DP / 2];
       const uint8_t* qrow = (t ? sQ1 : sQ0) + (row >> 3) * 1024 + (row & 7) * 128;
@@ -286,7 +315,7 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
         const uint4 v4 = *reinterpret_cast<const uint4*>(qrow + (u >> 3) * (BMQ * 128) + (((u & 7) ^ (row & 7)) << 4));
         qw[u * 4 + 0] = v4.x; qw[u * 4 + 1] = v4.y; qw[u * 4 + 2] = v4.z; qw[u * 4 + 3] = v4.w;
       }
-      const uint32_t q_addr = lane_addr + Q_COL0 + t * 128;
+      const uint32_t q_addr = lane_addr + SH::q_col(t);
       tmem_st_x32(q_addr, qw);
       if constexpr (DP / 2 > 32) tmem_st_x8(q_addr + 32, qw + 32);
       tmem_st_wait();
@@ -297,6 +326,14 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     // The K/V tile is consumed in NH half-steps of 64 keys: while this warp runs the softmax of one half, the
     // tensor core runs P·V of the previous half and Q·K^T of the same half of the NEXT tile, so S is (almost)
     // always ready when the warp comes back for it and the exponentials never wait for the tensor pipe.
+    // Ping-pong of the exponential phases: the two softmax warps of an SM sub-partition (same `quarter`, one per
+    // query tile) would otherwise lock in phase — both wait for S, then both queue on the MUFU unit (2 x 64 x 8 clk)
+    // while it idles for the ~400 clk of the S wait / load / P store.  A turn token (two named barriers per pair)
+    // makes them alternate: one warp's exponentials run under the other's wait + load + store and under the other
+    // tile's MMAs.  Tile 0 goes first; tile 1 posts the first token.
+    const bool pingpong = QT == 2 && n_qt == 2 && !(p.dbg & 2);
+    const int bar_mine = 1 + 2 * quarter + t, bar_other = 1 + 2 * quarter + (1 - t);
+    if (pingpong && t == 1) named_bar_arrive(bar_other, 64);
     int j = 0;
     for (int set = 0; set < p.n_sets; ++set) {
       float m_used = -INFINITY, l_run = 0.f;
@@ -308,6 +345,12 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
           mbar_wait(&s_full[t * 2 + hf], (uint32_t)(j & 1));
           tc_fence_after();
           mark(j * NH + hf, 1);
+          if (hf == NH - 1 && quarter == 0 && lane == 0) {
+            // S^{last half}(j) is complete, and the tensor pipe completes in issue order: every Q·K^T on K_j and
+            // every P·V on V_{j-1} of this tile is done — hand both stages back to the TMA producer
+            mbar_arrive(&k_empty[j % KV_STAGES]);
+            if (j > 0) mbar_arrive(&v_empty[(j - 1) % KV_STAGES]);
+          }
           uint32_t sr[HB];
           auto load_s = [&]() {
             tmem_ld_x32(sh_addr, sr);
@@ -370,7 +413,14 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
           }
           if constexpr (TRACE) asm volatile("" ::"f"(m_used) : "memory");
           mark(j * NH + hf, 3);
-          exp_pass(m_used * c);
+          // (ptxas moves arithmetic across bar instructions freely: the offset picks up a 0.0f that is read from
+          // shared memory behind the barrier, and the row sum is stored ahead of the arrive, so the exponentials
+          // stay inside the turn)
+          float moff = m_used * c;
+          if (pingpong) moff += named_bar_sync_ld(bar_mine, 64, pp_zero);
+          exp_pass(moff);
+          if (pingpong && !(t == 1 && set == p.n_sets - 1 && kt == n_kt - 1 && hf == NH - 1))
+            named_bar_arrive_st(bar_other, 64, pp_sink + (warp - 2), l_tile);   // (tile 1's last token: no taker)
           if (!first) {
             const bool grow = (m_tile - m_used) * c > RESCALE_LOG2;
             if (__any_sync(0xffffffffu, grow)) {
@@ -462,17 +512,19 @@ template <int DP, int BNK, int PF = 0, bool TRACE = false>
 int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p, int n_seq,
                 cudaStream_t st) {
   using C = ACfg<DP, BNK>;
+  constexpr int SMEM = C::SMEM;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(attn_sm100_kernel<DP, BNK, PF, TRACE>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    cudaError_t e = cudaFuncSetAttribute(attn_sm100_kernel<DP, BNK, PF, TRACE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     if (e != cudaSuccess) {
-      mdv2_set_error("attention_sm100: cannot set %d B dynamic smem: %s", C::SMEM, cudaGetErrorString(e));
+      mdv2_set_error("attention_sm100: cannot set %d B dynamic smem: %s", SMEM, cudaGetErrorString(e));
       return MDV2_ECUDA;
     }
     configured = true;
   }
-  dim3 grid((p.Lq + 2 * BMQ - 1) / (2 * BMQ), p.H, n_seq);
-  attn_sm100_kernel<DP, BNK, PF, TRACE><<<grid, NTHREADS, C::SMEM, st>>>(tq, tk, tv, p);
+  constexpr int QT = AShape<BNK>::QT;
+  dim3 grid((p.Lq + QT * BMQ - 1) / (QT * BMQ), p.H, n_seq);
+  attn_sm100_kernel<DP, BNK, PF, TRACE><<<grid, AShape<BNK>::NTHREADS, SMEM, st>>>(tq, tk, tv, p);
   MDV2_CHECK_LAUNCH("attention_sm100");
   return MDV2_OK;
 }

@@ -30,6 +30,25 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
 }
+// named barriers (ids 1..15; 0 is __syncthreads): `count` threads in total, syncing and arriving ones together
+__device__ __forceinline__ void named_bar_sync(int id, int count) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+__device__ __forceinline__ void named_bar_arrive(int id, int count) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+// the same with a memory dependence the compiler has to respect: a shared-memory word read behind the barrier /
+// written ahead of the arrive (arithmetic alone is moved across bar instructions)
+__device__ __forceinline__ float named_bar_sync_ld(int id, int count, const float* smem_word) {
+  float o;
+  asm volatile("bar.sync %1, %2;\n\tld.volatile.shared.f32 %0, [%3];"
+               : "=f"(o) : "r"(id), "r"(count), "r"(smem_u32(smem_word)) : "memory");
+  return o;
+}
+__device__ __forceinline__ void named_bar_arrive_st(int id, int count, float* smem_word, float v) {
+  asm volatile("st.volatile.shared.f32 [%2], %3;\n\tbar.arrive %0, %1;"
+               ::"r"(id), "r"(count), "r"(smem_u32(smem_word)), "f"(v) : "memory");
+}
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }

@@ -41,12 +41,13 @@ _lib.mdv2_unpatchify.argtypes = [_vp, _vp] + [_i32] * 10 + [_vp]
 _lib.mdv2_swap01.argtypes = [_vp, _vp, _i64, _i64, _i64, _vp]
 _lib.mdv2_scatter_runs.argtypes = [_vp, ctypes.POINTER(_vp), _i32, _i32, ctypes.POINTER(_i64), ctypes.POINTER(_i64),
                                    ctypes.POINTER(_i64), _i64, _i64, _vp]
-for _f in ("mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention", "mdv2_temporal_attention", "mdv2_patchify",
+_lib.mdv2_cfg_euler_step.argtypes = [_vp, _vp, _i32, _vp, _f32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _vp]
+for _f in ("mdv2_cfg_euler_step", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention", "mdv2_temporal_attention", "mdv2_patchify",
            "mdv2_unpatchify", "mdv2_swap01", "mdv2_scatter_runs"):
     getattr(_lib, _f).restype = _i32
 
 EXPORTS = ("mdv2_version", "mdv2_last_error", "mdv2_last_kernel", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention",
-           "mdv2_temporal_attention", "mdv2_patchify", "mdv2_unpatchify", "mdv2_swap01", "mdv2_scatter_runs")
+           "mdv2_temporal_attention", "mdv2_patchify", "mdv2_unpatchify", "mdv2_swap01", "mdv2_scatter_runs", "mdv2_cfg_euler_step")
 
 # kernel-launch counter (bench.py reports it as gpu_launches); +1 per C-ABI call that launches
 launches = 0
@@ -261,3 +262,32 @@ def scatter_runs(src, dst_ptrs, peer_dim, sizes, src_strides, dst_strides, run, 
     for x in sizes:
         nb *= x
     _t1(e0, "", 0, 2 * nb)
+
+
+def cfg_euler_step(pred, z, dt, guidance, x0=None, keep=None, z_in=None):
+    """Fused CFG combine + Euler update (+ frame-mask restore, + the next forward's doubled, cast input).
+
+    pred fp32 [2n, C, T, H, W] (cond half first), z [n, C, T, H, W] fp32 / bf16, dt fp32 [n] on the device,
+    keep bool/uint8 [n, T] with x0 (z's dtype) or both None, z_in optional [2n, C, T, H, W] fp32 / bf16.
+    Returns the fp32 z' (written in place when z is fp32)."""
+    n, C, T = z.shape[0], z.shape[1], z.shape[2]
+    hw = z.shape[3] * z.shape[4]
+    assert pred.dtype == torch.float32 and pred.is_contiguous() and pred.shape[0] == 2 * n
+    assert tuple(pred.shape[1:]) == tuple(z.shape[1:]) and z.is_contiguous()
+    assert dt.dtype == torch.float32 and dt.numel() == n and dt.is_contiguous()
+    z_out = z if z.dtype == torch.float32 else torch.empty_like(z, dtype=torch.float32)
+    if keep is not None:
+        assert x0 is not None and x0.dtype == z.dtype and x0.shape == z.shape and x0.is_contiguous()
+        keep = keep.to(torch.uint8).contiguous()
+        assert tuple(keep.shape) == (n, T)
+    if z_in is not None:
+        assert z_in.is_contiguous() and z_in.shape[0] == 2 * n and tuple(z_in.shape[1:]) == tuple(z.shape[1:])
+    e0 = _t0()
+    _check(_lib.mdv2_cfg_euler_step(_ptr(pred), _ptr(z), _dt(z), _ptr(dt), float(guidance),
+                                    _ptr(x0) if x0 is not None else None, _ptr(keep) if keep is not None else None,
+                                    _ptr(z_out), _ptr(z_in) if z_in is not None else None,
+                                    _dt(z_in) if z_in is not None else 0, n, C, T, hw, _stream()),
+           "mdv2_cfg_euler_step")
+    _t1(e0, "", 0, pred.numel() * 4 + z.numel() * (z.element_size() + 4)
+        + (z_in.numel() * z_in.element_size() if z_in is not None else 0))
+    return z_out

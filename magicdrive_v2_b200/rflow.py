@@ -1,0 +1,160 @@
+"""Rectified-flow sampler around the denoiser: the caller of the hot path.
+
+Mirror of ``magicdrivedit/schedulers/rf/__init__.py:13-115`` (``RFLOW``) and
+``magicdrivedit/schedulers/rf/rectified_flow.py:42-77,157-174`` (``timestep_transform``, ``add_noise``): same
+constructor keywords, same ``sample(model, text_encoder, z, prompts, device, ...)`` signature, same arithmetic.
+What changes is where the per-step glue runs: the whole schedule (timesteps, transformed timesteps, step sizes) is
+computed once and kept on the device, and the tail of every step — CFG combine, Euler update, frame-mask restore and
+the doubled, model-dtype input of the NEXT forward — is one launch of ``mdv2_cfg_euler_step`` instead of six eager
+passes over the latent (there is no CPU path: the latent must live on a CUDA device).
+"""
+from __future__ import annotations
+
+import torch
+
+from .registry import SCHEDULERS
+
+
+def timestep_transform(t, model_kwargs, base_resolution=512 * 512, base_num_frames=1, scale=1.0, num_timesteps=1,
+                       cog_style=False):
+    """rectified_flow.py:42-77 — resolution / length aware shift of the timestep, same op order and dtypes."""
+    for key in ["height", "width", "num_frames"]:
+        if model_kwargs[key].dtype == torch.float16:
+            model_kwargs[key] = model_kwargs[key].float()
+    t = t / num_timesteps
+    resolution = model_kwargs["height"] * model_kwargs["width"]
+    ratio_space = (resolution / base_resolution).sqrt()
+    if model_kwargs["num_frames"][0] == 1:
+        num_frames = torch.ones_like(model_kwargs["num_frames"])
+    elif cog_style:
+        num_frames = model_kwargs["num_frames"] // 4 + model_kwargs["num_frames"] % 2
+    else:
+        num_frames = model_kwargs["num_frames"] // 17 * 5
+    assert (num_frames >= 1).all(), "num_frames cannot be less than 1"
+    ratio_time = (num_frames / base_num_frames).sqrt()
+    ratio = ratio_space * ratio_time * scale
+    assert (ratio > 0).all(), "ratio cannot be 0"
+    new_t = ratio * t / (1 + (ratio - 1) * t)
+    return new_t * num_timesteps
+
+
+class RFlowScheduler:
+    """The part of rectified_flow.py:80-174 the sampler uses (constructor keywords + ``add_noise``)."""
+
+    def __init__(self, num_timesteps=1000, num_sampling_steps=10, use_discrete_timesteps=False,
+                 sample_method="uniform", loc=0.0, scale=1.0, use_timestep_transform=False, transform_scale=1.0,
+                 cog_style_trans=False):
+        assert sample_method in ["uniform", "logit-normal"]
+        assert sample_method == "uniform" or not use_discrete_timesteps, \
+            "Only uniform sampling is supported for discrete timesteps"
+        self.num_timesteps = num_timesteps
+        self.num_sampling_steps = num_sampling_steps
+        self.use_discrete_timesteps = use_discrete_timesteps
+        self.sample_method = sample_method
+        self.use_timestep_transform = use_timestep_transform
+        self.transform_scale = transform_scale
+        self.cog_style_trans = cog_style_trans
+
+    def add_noise(self, original_samples, noise, timesteps):
+        """rectified_flow.py:157-174."""
+        timepoints = 1 - timesteps.float() / self.num_timesteps
+        timepoints = timepoints[:, None, None, None, None]
+        return timepoints * original_samples + (1 - timepoints) * noise
+
+    def training_losses(self, *a, **k):
+        raise NotImplementedError("training is outside the denoising hot path (DESIGN.md §7)")
+
+
+@SCHEDULERS.register_module("rflow")
+class RFLOW:
+    def __init__(self, num_sampling_steps=10, num_timesteps=1000, cfg_scale=4.0, use_discrete_timesteps=False,
+                 use_timestep_transform=False, **kwargs):
+        self.num_sampling_steps = num_sampling_steps
+        self.num_timesteps = num_timesteps
+        self.cfg_scale = cfg_scale
+        self.use_discrete_timesteps = use_discrete_timesteps
+        self.use_timestep_transform = use_timestep_transform
+        self.scheduler = RFlowScheduler(num_timesteps=num_timesteps, num_sampling_steps=num_sampling_steps,
+                                        use_discrete_timesteps=use_discrete_timesteps,
+                                        use_timestep_transform=use_timestep_transform, **kwargs)
+
+    # -- schedule (rf/__init__.py:66-75,104-105), built once, resident on the device --------------------------
+    def schedule(self, n, device, additional_args=None):
+        ts = [(1.0 - i / self.num_sampling_steps) * self.num_timesteps for i in range(self.num_sampling_steps)]
+        if self.use_discrete_timesteps:
+            ts = [int(round(t)) for t in ts]
+        ts = [torch.tensor([t] * n, device=device) for t in ts]
+        if self.use_timestep_transform:
+            ts = [timestep_transform(t, additional_args, num_timesteps=self.num_timesteps,
+                                     cog_style=self.scheduler.cog_style_trans) for t in ts]
+        dts = [(ts[i] - ts[i + 1] if i < len(ts) - 1 else ts[i]) / self.num_timesteps for i in range(len(ts))]
+        return ts, torch.stack([d.float() for d in dts]).contiguous()
+
+    @torch.no_grad()
+    def sample(self, model, text_encoder, z, prompts, device, neg_prompts=None, additional_args=None, mask=None,
+               guidance_scale=None, progress=True):
+        from . import ops                                           # raises without libmdv2.so: no eager fallback
+        if guidance_scale is None:
+            guidance_scale = self.cfg_scale
+        n = len(prompts)
+        model_args = text_encoder.encode(prompts)
+        if neg_prompts is not None:
+            y_null = text_encoder.encode(neg_prompts)["y"]
+        else:
+            y_null = text_encoder.null(n).to(device)
+        model_args["y"] = torch.cat([model_args["y"], y_null], 0)
+        if additional_args is not None:
+            model_args.update(additional_args)
+
+        # The schedule is computed on the HOST (IEEE division; torch's CUDA kernels divide by a scalar through a
+        # rounded reciprocal, which would move timesteps by an ulp) and uploaded once.
+        host_args = None
+        if additional_args is not None:
+            host_args = {k: (v.cpu() if torch.is_tensor(v) else v) for k, v in additional_args.items()
+                         if k in ("height", "width", "num_frames")}
+        timesteps, dts = self.schedule(z.shape[0], "cpu", host_args)
+        keeps = [1 - t.float() / self.num_timesteps for t in timesteps]          # add_noise's timepoints
+        timesteps = [t.to(device) for t in timesteps]
+        keeps = [k.to(device)[:, None, None, None, None] for k in keeps]
+        dts = dts.to(device)
+        t2 = [torch.cat([t, t], 0) for t in timesteps]
+        if mask is not None:
+            noise_added = mask == 1
+
+        z = z.contiguous()
+        p0 = next(model.parameters(), None) if isinstance(model, torch.nn.Module) else None
+        in_dtype = p0.dtype if p0 is not None and p0.dtype in (torch.float32, torch.bfloat16) else torch.float32
+        z_in = torch.empty((2 * z.shape[0],) + tuple(z.shape[1:]), device=z.device, dtype=in_dtype)
+        z_in[: z.shape[0]].copy_(z)
+        z_in[z.shape[0]:].copy_(z)
+
+        steps = range(len(timesteps))
+        if progress:
+            try:
+                from tqdm import tqdm
+                steps = tqdm(steps, leave=False)
+            except ImportError:
+                pass
+        for i in steps:
+            t = timesteps[i]
+            x0 = keep = None
+            if mask is not None:                                    # rf/__init__.py:83-93
+                mask_t = mask * self.num_timesteps
+                x0 = z.clone()
+                x_noise = keeps[i] * x0 + (1 - keeps[i]) * torch.randn_like(x0)   # scheduler.add_noise(x0, noise, t)
+                keep = mask_t >= t.unsqueeze(1)
+                model_args["x_mask"] = keep.repeat(2, 1)
+                z = torch.where((keep & ~noise_added)[:, None, :, None, None], x_noise, x0).contiguous()
+                x0 = x0.to(z.dtype)
+                noise_added = keep
+                z_in[: z.shape[0]].copy_(z)
+                z_in[z.shape[0]:].copy_(z)
+            pred = model(z_in, t2[i], **model_args)
+            if pred.shape[1] == z_in.shape[1] * 2:
+                pred = pred.chunk(2, dim=1)[0]
+            else:
+                assert pred.shape[1] == z_in.shape[1]
+            pred = pred.float().contiguous()
+            z = ops.cfg_euler_step(pred, z, dts[i], guidance_scale, x0=x0, keep=keep,
+                                   z_in=None if mask is not None else z_in)
+        return z

@@ -56,3 +56,21 @@ def build_reference_model(kwargs: dict, brushnet: bool = False):
     cfg = ref.MagicDriveSTDiT3Config(**kwargs)
     cls = ref.MagicDriveSTDiT3BrushNet if brushnet else ref.MagicDriveSTDiT3
     return cls(cfg)
+
+
+def load_reference_sampler():
+    """Returns the reference module ``magicdrivedit.schedulers.rf`` (RFLOW, timestep_transform)."""
+    load_reference()
+    name = "magicdrivedit.schedulers.rf"
+    if name in sys.modules:
+        return sys.modules[name]
+    pkg = os.path.join(REF_ROOT, "magicdrivedit")
+    _ns("magicdrivedit.schedulers", os.path.join(pkg, "schedulers"))      # skip iddpm / dpm-solver imports
+    iu = types.ModuleType("magicdrivedit.utils.inference_utils")          # pulls mmcv / datasets; sample() never calls it
+
+    def replace_with_null_condition(*a, **k):
+        raise NotImplementedError("oracle stub")
+
+    iu.replace_with_null_condition = replace_with_null_condition
+    sys.modules.setdefault("magicdrivedit.utils.inference_utils", iu)
+    return importlib.import_module(name)

@@ -41,3 +41,64 @@ class use_ops:
 
     def __exit__(self, *a):
         MagicDriveSTDiT3._ops = self.prev
+
+
+# ---- sampler fixtures (shared by oracle/make_golden_rflow.py and the rflow tests) ------------------------------
+class ToyDenoiser(torch.nn.Module):
+    """Stand-in denoiser built from separately rounded fp32 multiplies and adds only, so CPU and GPU agree to the
+    bit: enough to pin the sampler's own arithmetic (schedule, CFG, Euler, mask) against the reference."""
+
+    def __init__(self, dtype=torch.bfloat16):
+        super().__init__()
+        self.w = torch.nn.Parameter(torch.tensor(0.3, dtype=dtype))
+
+    def forward(self, x, timestep, y, x_mask=None, **kwargs):
+        xf = x.to(self.w.dtype).float()
+        s = y.float().view(-1, 1, 1, 1, 1)
+        tt = (timestep.float() * 0.001).view(-1, 1, 1, 1, 1)      # (no division: CUDA divides through a reciprocal)
+        out = xf * 0.3
+        out = out + s * tt
+        if x_mask is not None:
+            out = out * x_mask[:, None, :, None, None].float()
+            out = out + 0.125
+        return out
+
+
+class ToyTextEncoder:
+    def encode(self, prompts):
+        return dict(y=torch.tensor([0.5 + 0.25 * i for i in range(len(prompts))]))
+
+    def null(self, n):
+        return torch.full((n,), -0.75)
+
+
+RFLOW_CASES = {
+    # name: (scheduler kwargs, z shape [n, C, T, H, W], z dtype, mask rows or None, guidance)
+    "plain": (dict(num_sampling_steps=4, cfg_scale=4.0), (2, 6, 3, 5, 8), torch.float32, None, None),
+    "cog_bf16": (dict(num_sampling_steps=5, cfg_scale=2.0, use_timestep_transform=True, cog_style_trans=True),
+                 (2, 12, 5, 6, 7), torch.bfloat16, None, None),
+    "masked": (dict(num_sampling_steps=6, cfg_scale=2.0, use_timestep_transform=True, cog_style_trans=True),
+               (2, 6, 5, 4, 8), torch.bfloat16, [[0.0, 1, 1, 0.5, 1], [1, 1, 0.25, 1, 0]], 3.0),
+}
+
+
+def rflow_inputs(name, device="cpu"):
+    kw, shape, dtype, mask, g = RFLOW_CASES[name]
+    gen = torch.Generator().manual_seed(7)
+    z = torch.randn(shape, generator=gen).to(dtype).to(device)
+    n = shape[0]
+    extra = dict(height=torch.tensor([848.0] * n, dtype=dtype, device=device),
+                 width=torch.tensor([1600.0] * n, dtype=dtype, device=device),
+                 num_frames=torch.tensor([17.0] * n, dtype=dtype, device=device))
+    mask_t = torch.tensor(mask, device=device) if mask is not None else None
+    return kw, z, extra, mask_t, g
+
+
+class cpu_randn_like:
+    """torch.randn_like drawn from a seeded CPU generator wherever the tensor lives (tests only)."""
+
+    def __init__(self, seed=11):
+        self.gen = torch.Generator().manual_seed(seed)
+
+    def __call__(self, x):
+        return torch.randn(x.shape, generator=self.gen, dtype=x.dtype).to(x.device)
