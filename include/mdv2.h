@@ -99,6 +99,30 @@ int mdv2_scatter_runs(const void* src, void* const* dst_ptrs, int n_dst, int pee
                       const int64_t* src_strides, const int64_t* dst_strides, int64_t run_bytes, int64_t dst_base,
                       void* stream);
 
+/* qkv projection + per-head RMSNorm of q and k (as mdv2_gemm with rms_q / rms_k) whose epilogue stores head group g of
+ * each of q | k | v (N = 3·W columns, groups of W / n_dst columns) straight into dst_ptrs[g] — the ranks of a
+ * sequence-parallel group, mapped through NVLink peer memory — in the layout mdv2_attention reads there:
+ *   dst_ptrs[g] [seq][rank·rows_per_seq + r][q|k|v][W / n_dst],   seq = row / rows_per_seq, r = row % rows_per_seq.
+ * The GEMM and the head-scatter / sequence-gather all-to-all are one kernel: the NVLink stores ride under the MMAs.
+ * Replaces qkv Linear + q_norm / k_norm + all_to_all (+ split / cat / rearrange) of SeqParallelMultiHeadAttention,
+ * magicdrivedit/models/layers/blocks.py:554-600 and acceleration/communications.py:11-66.  bf16, sm_100a only; the
+ * caller orders it against the peers (group barrier behind the launch). */
+int mdv2_gemm_qkv_scatter(const void* a, int64_t lda, const void* w, int64_t ldw, const void* bias, int64_t M, int N,
+                          int K, const void* rms_q, const void* rms_k, int head_dim, float eps,
+                          void* const* dst_ptrs, int n_dst, int rows_per_seq, int rank, void* stream);
+
+/* mdv2_attention whose epilogue stores the final (normalised, summed over K/V sets) output row s of sequence i straight
+ * into the rank that owns it under sequence parallelism:  dst_ptrs[s / rows_per_rank] [(i·rows_per_rank +
+ * s % rows_per_rank)·dst_ld + dst_col + h·D : + D]  (Lq = n_dst·rows_per_rank; dst_col = this rank's head-group column).
+ * `partial` [n_seq·Lq, ldp] only carries the running sum of earlier K/V sets (may be NULL when n_sets == 1).
+ * Attention and the sequence-scatter / head-gather all-to-all are one kernel.  Replaces flash_attn_func + all_to_all
+ * (+ rearranges) of SeqParallelMultiHeadAttention, magicdrivedit/models/layers/blocks.py:607-638 and
+ * acceleration/communications.py:11-66.  bf16, sm_100a only; the caller orders it against the peers. */
+int mdv2_attention_scatter(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                           void* partial, int64_t ldp, int n_seq, int Lq, int Lk, int H, int D, float scale,
+                           const int32_t* kv_map, int n_sets, void* const* dst_ptrs, int n_dst, int rows_per_rank,
+                           int64_t dst_ld, int dst_col, void* stream);
+
 /* Tail of one RFLOW sampling step (magicdrivedit/schedulers/rf/__init__.py:100-109) plus the head of the next
  * (:95 and the x.to(dtype) of magicdrive_stdit3.py:1041), fused into one pass:
  *   v = pred[n:] + guidance * (pred[:n] - pred[n:]);  z_out = z + v * dt[b]        (fp32, each op rounded separately)

@@ -99,9 +99,12 @@ class STDiT3Block(nn.Module):
 
         # (b) LN -> modulate ; (c) self-attention ; (d) gated residual.  The projections on either side of a
         # spatial attention are handed over as row-range callbacks (see MagicDriveSTDiT3._spatial_attention).
-        def qkv_rows(rows, tab):
+        def qkv_rows(rows, tab, scatter=None):
             ops.ln_modulate(x[rows], ws.xm[rows], tab(mod), 0, 1, geo)
-            ops.gemm(ws.xm[rows], a.qkv.weight, a.qkv.bias, ws.qkv[rows], geo=geo, rms=(qn, kn, D, C, C))
+            if scatter is not None:                     # sequence parallel: the epilogue stores into the peers' HBM
+                ops.gemm_qkv_scatter(ws.xm[rows], a.qkv.weight, a.qkv.bias, (qn, kn, D, C, C), *scatter)
+            else:
+                ops.gemm(ws.xm[rows], a.qkv.weight, a.qkv.bias, ws.qkv[rows], geo=geo, rms=(qn, kn, D, C, C))
 
         def proj_rows(rows, tab):
             ops.gemm(ws.ao[rows], a.proj.weight, a.proj.bias, x[rows], geo=geo, gate=(tab(mod), 2), res=x[rows])
@@ -130,10 +133,13 @@ class STDiT3Block(nn.Module):
             cv = self.cross_view_attn
             n_nbr = float(ctx.kv_map.shape[1])
 
-            def cv_qkv_rows(rows, tab):
+            def cv_qkv_rows(rows, tab, scatter=None):
                 ops.ln_modulate(x[rows], ws.xm[rows], tab(mod_mva), 0, 1, geo)
-                ops.gemm(ws.xm[rows], cv.qkv.weight, None, ws.qkv[rows], geo=geo,
-                         rms=(cv.q_norm.weight, cv.k_norm.weight, D, C, C))
+                rms = (cv.q_norm.weight, cv.k_norm.weight, D, C, C)
+                if scatter is not None:
+                    ops.gemm_qkv_scatter(ws.xm[rows], cv.qkv.weight, None, rms, *scatter)
+                else:
+                    ops.gemm(ws.xm[rows], cv.qkv.weight, None, ws.qkv[rows], geo=geo, rms=rms)
 
             def cv_proj_rows(rows, tab):
                 # proj(a0) + proj(a1) = W(a0 + a1) + n_nbr·bias ; then gate ; then mva_proj + residual

@@ -8,7 +8,7 @@ bool mdv2_attention_sm100_supported(int64_t ldq, int64_t ldk, int64_t ldv, int64
                                     int n_sets);
 int mdv2_attention_sm100(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                          void* out, int64_t ldo, int n_seq, int Lq, int Lk, int H, int D, float scale,
-                         const int32_t* kv_map, int n_sets, cudaStream_t st);
+                         const int32_t* kv_map, int n_sets, cudaStream_t st, const AttnScatter* scatter = nullptr);
 
 static bool device_is_sm100() {
   static int cached = -1;
@@ -85,6 +85,38 @@ extern "C" int mdv2_gemm(const void* a, int64_t lda, const void* w, int64_t ldw,
   if (rc) return rc;
   if (has_rms) return mdv2_qk_rmsnorm(out, ldo, M, head_dim, n_q, n_k, rms_q, rms_k, eps, dtype, st);
   return MDV2_OK;
+}
+
+extern "C" int mdv2_gemm_qkv_scatter(const void* a, int64_t lda, const void* w, int64_t ldw, const void* bias,
+                                     int64_t M, int N, int K, const void* rms_q, const void* rms_k, int head_dim,
+                                     float eps, void* const* dst_ptrs, int n_dst, int rows_per_seq, int rank,
+                                     void* stream) {
+  if (M == 0 || N == 0) return MDV2_OK;
+  MDV2_REQUIRE(M > 0 && N > 0 && K > 0 && N % 3 == 0, "gemm_qkv_scatter: bad shape M=%lld N=%d K=%d", (long long)M, N, K);
+  MDV2_REQUIRE(rms_q && rms_k && head_dim > 0 && dst_ptrs && n_dst >= 1 && n_dst <= 8, "gemm_qkv_scatter: bad arguments");
+  // there is no SIMT flavour of the fused scatter: the caller falls back to mdv2_gemm + mdv2_scatter_runs
+  MDV2_REQUIRE(device_is_sm100(), "gemm_qkv_scatter: needs sm_100a");
+  RmsArgs rms{rms_q, rms_k, head_dim, N / 3, N / 3, eps};
+  MDV2_REQUIRE(mdv2_gemm_sm100_supported(M, N, K, lda, ldw, 8, &rms), "gemm_qkv_scatter: shape not tiled by the tcgen05 kernel");
+  Epilogue<bf16> ep = make_epilogue<bf16>(bias, 1.f, 0, nullptr, 0, 0, nullptr, 0, 0, 1, 1, 1, 1, N);
+  QkvScatter sc{dst_ptrs, n_dst, rows_per_seq, rank};
+  return mdv2_gemm_sm100(a, lda, w, ldw, nullptr, 8, M, N, K, ep, &rms, (cudaStream_t)stream, &sc);
+}
+
+extern "C" int mdv2_attention_scatter(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                                      void* partial, int64_t ldp, int n_seq, int Lq, int Lk, int H, int D, float scale,
+                                      const int32_t* kv_map, int n_sets, void* const* dst_ptrs, int n_dst,
+                                      int rows_per_rank, int64_t dst_ld, int dst_col, void* stream) {
+  if (n_seq == 0 || Lq == 0) return MDV2_OK;
+  MDV2_REQUIRE(n_seq > 0 && Lq > 0 && Lk > 0 && H > 0 && D > 0, "attention_scatter: bad shape");
+  MDV2_REQUIRE(n_sets >= 1 && (kv_map != nullptr || n_sets == 1), "attention_scatter: n_sets > 1 needs kv_map");
+  MDV2_REQUIRE(dst_ptrs != nullptr && (n_sets == 1 || partial != nullptr), "attention_scatter: missing buffers");
+  // bf16 / tcgen05 only: other shapes go through mdv2_attention + mdv2_scatter_runs
+  MDV2_REQUIRE(device_is_sm100() && mdv2_attention_sm100_supported(ldq, ldk, ldv, ldp, Lq, Lk, H, D, n_sets),
+               "attention_scatter: shape not taken by the tcgen05 kernel");
+  AttnScatter sc{dst_ptrs, n_dst, rows_per_rank, dst_col, dst_ld};
+  return mdv2_attention_sm100(q, ldq, k, ldk, v, ldv, partial, ldp, n_seq, Lq, Lk, H, D, scale, kv_map, n_sets,
+                              (cudaStream_t)stream, &sc);
 }
 
 extern "C" int mdv2_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,

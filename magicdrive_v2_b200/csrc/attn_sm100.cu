@@ -70,6 +70,12 @@ struct AParams {
   int Lq, Lk, H, D, n_sets;
   float scale_log2;
   const int32_t* kv_map;
+  // sequence parallelism: the normalised output rows of the LAST K/V set go straight to the rank that owns the row
+  // (peer-mapped [n_seq·rows_per_rank, peer_ld] buffers, this rank's head group at column peer_col); `out` then only
+  // carries the running sum of earlier sets.  n_peer == 0: everything goes to `out`.
+  bf16* peer_out[8];
+  int n_peer, rows_per_rank, peer_col;
+  int64_t peer_ld;
   long long* trace;        // debug timeline (tools/attn_trace.py) or nullptr
   int dbg;                 // debug switches (MDV2_ATTN_DBG): bit 0 swaps the TMA / MMA warps, bit 1 disables the ping-pong
 };
@@ -304,6 +310,12 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     const int q_idx = q_row0 + t * BMQ + row;
     const float c = p.scale_log2;
     bf16* orow = p.out + ((int64_t)seq * p.Lq + q_idx) * p.ldo + (int64_t)h * p.D;
+    bf16* frow = orow;                                 // where the final (last set) output row goes
+    if (p.n_peer > 0 && q_idx < p.Lq) {
+      const int owner = q_idx / p.rows_per_rank;
+      frow = p.peer_out[owner] + ((int64_t)seq * p.rows_per_rank + (q_idx - owner * p.rows_per_rank)) * p.peer_ld +
+             p.peer_col + (int64_t)h * p.D;
+    }
     {
       // Q_t: this thread's row from the 128-byte-swizzled TMA tile (16-byte unit u of row r sits at u ^ (r % 8))
       // -> TMEM columns q_col(t) .. (+ DP/2), the A-operand layout (lane = row, bf16 pairs along K)
@@ -488,7 +500,7 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
                     for (int i = 0; i < 8; ++i) a[i] += gg[i];
                     o.pack(a);
                   }
-                  *reinterpret_cast<uint4*>(orow + d) = o.raw;
+                  *reinterpret_cast<uint4*>((set == p.n_sets - 1 ? frow : orow) + d) = o.raw;
                 }
               }
             }
@@ -543,11 +555,12 @@ bool mdv2_attention_sm100_supported(int64_t ldq, int64_t ldk, int64_t ldv, int64
 
 int mdv2_attention_sm100(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                          void* out, int64_t ldo, int n_seq, int Lq, int Lk, int H, int D, float scale,
-                         const int32_t* kv_map, int n_sets, cudaStream_t st) {
+                         const int32_t* kv_map, int n_sets, cudaStream_t st, const AttnScatter* scatter) {
   MDV2_REQUIRE(mdv2_attention_sm100_supported(ldq, ldk, ldv, ldo, Lq, Lk, H, D, n_sets), "attention_sm100: unsupported shape");
   MDV2_REQUIRE(n_seq <= 65535, "attention_sm100: too many sequences");
   MDV2_REQUIRE(((uintptr_t)q % 16 == 0) && ((uintptr_t)k % 16 == 0) && ((uintptr_t)v % 16 == 0) && ((uintptr_t)out % 16 == 0),
                "attention_sm100: operands must be 16-byte aligned");
+  MDV2_REQUIRE(out != nullptr || (scatter != nullptr && n_sets == 1), "attention_sm100: missing output");
   const int bnk = Lk <= 64 ? 64 : 128;
   CUtensorMap tq, tk, tv;
   int rc = mdv2_make_tmap_3d_heads(&tq, q, (uint64_t)n_seq * Lq, H, D, ldq, BMQ);
@@ -563,6 +576,20 @@ int mdv2_attention_sm100(const void* q, int64_t ldq, const void* k, int64_t ldk,
   p.Lq = Lq; p.Lk = Lk; p.H = H; p.D = D; p.n_sets = n_sets;
   p.scale_log2 = scale * 1.4426950408889634f;
   p.kv_map = kv_map;
+  p.n_peer = 0;
+  if (scatter != nullptr) {
+    MDV2_REQUIRE(scatter->n_dst >= 1 && scatter->n_dst <= 8 && scatter->rows_per_rank > 0 &&
+                     (int64_t)scatter->n_dst * scatter->rows_per_rank == Lq && scatter->dst_ld % 8 == 0 &&
+                     scatter->dst_col % 8 == 0,
+                 "attention_sm100: bad output scatter geometry");
+    p.n_peer = scatter->n_dst;
+    p.rows_per_rank = scatter->rows_per_rank;
+    p.peer_ld = scatter->dst_ld;
+    p.peer_col = scatter->dst_col;
+    for (int i = 0; i < 8; ++i) p.peer_out[i] = i < scatter->n_dst ? (bf16*)scatter->dst[i] : nullptr;
+    for (int i = 0; i < scatter->n_dst; ++i)
+      MDV2_REQUIRE(scatter->dst[i] != nullptr && (uintptr_t)scatter->dst[i] % 16 == 0, "attention_sm100: bad scatter destination");
+  }
   p.trace = g_attn_trace;
   static const int dbg = [] {
     const char* e = getenv("MDV2_ATTN_DBG");

@@ -106,3 +106,10 @@ static inline int mdv2_num_sms() {
   }
   return n;
 }
+
+// output scatter of the tcgen05 attention kernel under sequence parallelism (see AParams in attn_sm100.cu)
+struct AttnScatter {
+  void* const* dst;
+  int n_dst, rows_per_rank, dst_col;
+  int64_t dst_ld;
+};

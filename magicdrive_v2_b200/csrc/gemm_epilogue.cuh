@@ -53,5 +53,11 @@ struct RmsArgs {
   float eps;
 };
 bool mdv2_gemm_sm100_supported(int64_t M, int N, int K, int64_t lda, int64_t ldw, int64_t ldo, const RmsArgs* rms);
+// scattered qkv output (sequence parallelism): destinations = the peers' [seq][n_dst·rows_per_seq][3][W/n_dst] buffers
+struct QkvScatter {
+  void* const* dst;
+  int n_dst, rows_per_seq, rank;
+};
 int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void* out, int64_t ldo, int64_t M, int N,
-                    int K, const Epilogue<bf16>& ep, const RmsArgs* rms, cudaStream_t st);
+                    int K, const Epilogue<bf16>& ep, const RmsArgs* rms, cudaStream_t st,
+                    const QkvScatter* scatter = nullptr);

@@ -44,7 +44,20 @@ struct Cfg {
   static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-B alignment");
 };
 
+// Optional scattered output of the qkv projection under sequence parallelism (HD != 0 flavour only): the N = 3·W
+// output columns are q | k | v of width W; head group g = (col % W) / grp of every part goes to dst[g] (the peers of a
+// sequence-parallel group, mapped through NVLink) in the layout the attention kernel reads,
+//   dst[g][seq][row_base + r][part][grp]   with seq = row / rows_per_seq, r = row % rows_per_seq,
+// i.e. the head-scatter / sequence-gather all-to-all is done by the epilogue's own stores, under the MMAs.
+struct ScatterOut {
+  bf16* dst[8];
+  int n_dst;                 // 0: plain output
+  int grp, part_w, rows_per_seq;
+  int64_t dst_ld, seq_rows, row_base;
+};
+
 struct Params {
+  ScatterOut sc;
   int64_t M;
   int N, K;
   int64_t ldo;
@@ -180,6 +193,12 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         const RowCtx rc = ep.row_ctx(gr < p.M ? gr : 0);
         row_res[lane] = rc.res_row * ep.ldr;
         row_gate[lane] = rc.gate ? (int64_t)(rc.gate - ep.gate_mod) : -1;
+        if constexpr (HD != 0) {
+          if (p.sc.n_dst > 0) {                      // destination row of the scattered qkv output
+            const int64_t g = gr < p.M ? gr : 0, sq = g / p.sc.rows_per_seq;
+            row_res[lane] = (sq * p.sc.seq_rows + p.sc.row_base + (g - sq * p.sc.rows_per_seq)) * p.sc.dst_ld;
+          }
+        }
       }
 #pragma unroll
       for (int ci = 0; ci < CPW; ++ci) {
@@ -273,6 +292,13 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         __syncwarp();
         // column phase: coalesced 16-byte accesses: gate / residual / store
+        bf16* sc_base = nullptr;                     // scattered output: this chunk (= one head) has one destination
+        if constexpr (HD != 0) {
+          if (p.sc.n_dst > 0) {
+            const int part = c0 / p.sc.part_w, cc = c0 - part * p.sc.part_w, g = cc / p.sc.grp;
+            sc_base = p.sc.dst[g] + part * p.sc.grp + (cc - g * p.sc.grp);
+          }
+        }
 #pragma unroll
         for (int it = 0; it < NIT; ++it) {
           const int idx = lane + 32 * it, rl = idx / UPR, u = idx % UPR;
@@ -304,7 +330,11 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               }
               pk.pack(f);
             }
-            *reinterpret_cast<uint4*>(p.out + gr * p.ldo + col) = pk.raw;
+            bf16* optr = p.out + gr * p.ldo + col;
+            if constexpr (HD != 0) {
+              if (sc_base != nullptr) optr = sc_base + row_res[rl] + u * 8;
+            }
+            *reinterpret_cast<uint4*>(optr) = pk.raw;
           }
         }
         __syncwarp();
@@ -433,7 +463,7 @@ bool mdv2_gemm_sm100_supported(int64_t M, int N, int K, int64_t lda, int64_t ldw
 }
 
 int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void* out, int64_t ldo, int64_t M, int N,
-                    int K, const Epilogue<bf16>& ep, const RmsArgs* rms, cudaStream_t st) {
+                    int K, const Epilogue<bf16>& ep, const RmsArgs* rms, cudaStream_t st, const QkvScatter* scatter) {
   MDV2_REQUIRE(mdv2_gemm_sm100_supported(M, N, K, lda, ldw, ldo, rms), "gemm_sm100: unsupported shape M=%lld N=%d K=%d",
                (long long)M, N, K);
   MDV2_REQUIRE(((uintptr_t)a % 16 == 0) && ((uintptr_t)w % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
@@ -446,6 +476,26 @@ int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void
   rc = mdv2_make_tmap_2d(&tw, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)bn / 2, BK);
   if (rc) return rc;
   Params p;
+  p.sc.n_dst = 0;
+  if (scatter != nullptr) {
+    const int hd = rms ? rms->head_dim : 0;
+    MDV2_REQUIRE(rms && rms->wq && (bn == 144 || bn == 128) && N % 3 == 0, "gemm_sm100: scattered output needs the RMSNorm qkv flavour");
+    const int W = N / 3;
+    MDV2_REQUIRE(scatter->n_dst >= 1 && scatter->n_dst <= 8 && W % scatter->n_dst == 0 && (W / scatter->n_dst) % hd == 0 &&
+                     rms->n_q == W && rms->n_k == W && scatter->rows_per_seq > 0 && M % scatter->rows_per_seq == 0 &&
+                     scatter->rank >= 0 && scatter->rank < scatter->n_dst,
+                 "gemm_sm100: bad scatter geometry");
+    p.sc.n_dst = scatter->n_dst;
+    p.sc.grp = W / scatter->n_dst;
+    p.sc.part_w = W;
+    p.sc.rows_per_seq = scatter->rows_per_seq;
+    p.sc.dst_ld = 3 * (int64_t)p.sc.grp;
+    p.sc.seq_rows = (int64_t)scatter->n_dst * scatter->rows_per_seq;
+    p.sc.row_base = (int64_t)scatter->rank * scatter->rows_per_seq;
+    for (int i = 0; i < 8; ++i) p.sc.dst[i] = i < scatter->n_dst ? (bf16*)scatter->dst[i] : nullptr;
+    for (int i = 0; i < scatter->n_dst; ++i)
+      MDV2_REQUIRE(scatter->dst[i] != nullptr && (uintptr_t)scatter->dst[i] % 16 == 0, "gemm_sm100: bad scatter destination");
+  }
   p.M = M; p.N = N; p.K = K; p.ldo = ldo; p.out = (bf16*)out; p.ep = ep;
   p.rms_q = rms ? (const bf16*)rms->wq : nullptr;
   p.rms_k = rms ? (const bf16*)rms->wk : nullptr;

@@ -42,12 +42,17 @@ _lib.mdv2_swap01.argtypes = [_vp, _vp, _i64, _i64, _i64, _vp]
 _lib.mdv2_scatter_runs.argtypes = [_vp, ctypes.POINTER(_vp), _i32, _i32, ctypes.POINTER(_i64), ctypes.POINTER(_i64),
                                    ctypes.POINTER(_i64), _i64, _i64, _vp]
 _lib.mdv2_cfg_euler_step.argtypes = [_vp, _vp, _i32, _vp, _f32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i64, _vp]
-for _f in ("mdv2_cfg_euler_step", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention", "mdv2_temporal_attention", "mdv2_patchify",
+_lib.mdv2_gemm_qkv_scatter.argtypes = [_vp, _i64, _vp, _i64, _vp, _i64, _i32, _i32, _vp, _vp, _i32, _f32,
+                                       ctypes.POINTER(_vp), _i32, _i32, _i32, _vp]
+_lib.mdv2_attention_scatter.argtypes = [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _f32,
+                                        _vp, _i32, ctypes.POINTER(_vp), _i32, _i32, _i64, _i32, _vp]
+for _f in ("mdv2_attention_scatter", "mdv2_gemm_qkv_scatter", "mdv2_cfg_euler_step", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention", "mdv2_temporal_attention", "mdv2_patchify",
            "mdv2_unpatchify", "mdv2_swap01", "mdv2_scatter_runs"):
     getattr(_lib, _f).restype = _i32
 
 EXPORTS = ("mdv2_version", "mdv2_last_error", "mdv2_last_kernel", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention",
-           "mdv2_temporal_attention", "mdv2_patchify", "mdv2_unpatchify", "mdv2_swap01", "mdv2_scatter_runs", "mdv2_cfg_euler_step")
+           "mdv2_temporal_attention", "mdv2_patchify", "mdv2_unpatchify", "mdv2_swap01", "mdv2_scatter_runs", "mdv2_cfg_euler_step", "mdv2_gemm_qkv_scatter",
+           "mdv2_attention_scatter")
 
 # kernel-launch counter (bench.py reports it as gpu_launches); +1 per C-ABI call that launches
 launches = 0
@@ -291,3 +296,53 @@ def cfg_euler_step(pred, z, dt, guidance, x0=None, keep=None, z_in=None):
     _t1(e0, "", 0, pred.numel() * 4 + z.numel() * (z.element_size() + 4)
         + (z_in.numel() * z_in.element_size() if z_in is not None else 0))
     return z_out
+
+
+def gemm_qkv_scatter_supported(a, w, head_dim, p) -> bool:
+    """The fused projection + scatter exists for the bf16 tcgen05 kernel with whole heads per rank."""
+    N = w.shape[0]
+    return (a.dtype == torch.bfloat16 and default_backend != BACKEND_SIMT and head_dim in (64, 72) and N % 3 == 0
+            and (N // 3) % p == 0 and ((N // 3) // p) % head_dim == 0 and a.shape[1] % 64 == 0 and p <= 8)
+
+
+def gemm_qkv_scatter(a, w, bias, rms, dst_ptrs, rows_per_seq, rank):
+    """qkv = RMSNorm_qk(a @ w.T + bias), head group g of q | k | v stored into ``dst_ptrs[g]`` (raw device addresses
+    of the peers' ``[seq, p·rows_per_seq, 3, W/p]`` buffers) at sequence rows ``rank·rows_per_seq + r``."""
+    wq, wk, D, n_q, n_k = rms
+    M, K = a.shape
+    N = w.shape[0]
+    assert n_q == n_k == N // 3 and w.shape[1] == K and M % rows_per_seq == 0
+    pa, lda = _rows2d(a)
+    pw, ldw = _rows2d(w)
+    n = len(dst_ptrs)
+    arr = (_vp * n)(*[_vp(int(q)) for q in dst_ptrs])
+    e0 = _t0()
+    _check(_lib.mdv2_gemm_qkv_scatter(pa, lda, pw, ldw, _ptr(bias, a.dtype) if bias is not None else None, M, N, K,
+                                      _ptr(wq, a.dtype), _ptr(wk, a.dtype), D, 1e-6, arr, n, rows_per_seq, rank,
+                                      _stream()), "mdv2_gemm_qkv_scatter")
+    _t1(e0, "", 2.0 * M * N * K, (M * K + N * K + M * N) * a.element_size())
+
+
+def attention_scatter_supported(q, D, p) -> bool:
+    return q.dtype == torch.bfloat16 and default_backend != BACKEND_SIMT and D in (64, 72) and p <= 8
+
+
+def attention_scatter(q, k, v, partial, n_seq, Lq, Lk, H, D, scale, dst_ptrs, rows_per_rank, dst_ld, dst_col,
+                      kv_map=None):
+    """``attention`` whose final output rows go straight into ``dst_ptrs[row // rows_per_rank]`` (the peers' ``[N_l, C]``
+    buffers, this rank's head group at column ``dst_col``); ``partial`` holds the sum of earlier K/V sets."""
+    pq, ldq = _rows2d(q)
+    pk, ldk = _rows2d(k)
+    pv, ldv = _rows2d(v)
+    n_sets = 1 if kv_map is None else kv_map.shape[1]
+    pp, ldp = _rows2d(partial)
+    pm = _ptr(kv_map, torch.int32) if kv_map is not None else None
+    n = len(dst_ptrs)
+    arr = (_vp * n)(*[_vp(int(a)) for a in dst_ptrs])
+    e0 = _t0()
+    _check(_lib.mdv2_attention_scatter(pq, ldq, pk, ldk, pv, ldv, pp, ldp, n_seq, Lq, Lk, H, D, float(scale), pm,
+                                       n_sets, arr, n, rows_per_rank, dst_ld, dst_col, _stream()),
+           "mdv2_attention_scatter")
+    tag = "[xview]" if n_sets > 1 else "[self]"
+    _t1(e0, tag, 4.0 * n_seq * Lq * Lk * H * D * n_sets,
+        (2 * q.shape[0] + 2 * n_sets * n_seq * Lk) * H * D * q.element_size())

@@ -190,11 +190,24 @@ def symm_buffer(tag, shape, like, group):
     return ent
 
 
+stats = {"fused_qkv_scatter": 0, "fused_out_scatter": 0, "scatter_kernel": 0}     # which exchange ran (tests check the path taken)
+
+
+def _fused_scatter(ops, qkv, D, C, p) -> bool:
+    """GEMM-epilogue scatter of q|k|v (``MDV2_SP_FUSED=0`` keeps the separate scatter kernel)."""
+    import os
+    if os.environ.get("MDV2_SP_FUSED", "1") == "0" or not hasattr(ops, "gemm_qkv_scatter"):
+        return False
+    return (qkv.dtype == torch.bfloat16 and D in (64, 72) and (C // p) % D == 0 and C % 64 == 0
+            and getattr(ops, "default_backend", 0) != getattr(ops, "BACKEND_SIMT", 1))
+
+
 def ulysses_attention_peer(ops, qkv, ao_sym, d, kv_map, scale, group, p, rank, produce, consume):
     """Same contract as ``ulysses_attention`` over peer memory.  ``ao_sym = (tensor, handle, peer addresses)`` is
     the symmetric buffer that ``consume`` reads the attention output from (the workspace's ``ao``).
 
-        produce -> scatter(q|k|v heads -> owner ranks, straight into [β·T, S, 3, Hp·D]) -> barrier -> attention
+        produce (+ scatter of q|k|v heads -> owner ranks, straight into [β·T, S, 3, Hp·D], fused into the qkv
+                 GEMM's epilogue when the tcgen05 kernel takes the shape) -> barrier -> attention
                 -> scatter(output rows -> owner ranks, straight into their [N_l, C]) -> barrier -> consume
 
     No pack / unpack copies and no NCCL call: the scatter kernel reads local HBM once and writes the peers'
@@ -206,19 +219,34 @@ def ulysses_attention_peer(ops, qkv, ao_sym, d, kv_map, scale, group, p, rank, p
     BT = d.B * d.T
     rows = slice(0, d.N)
     ident = lambda m: m                                   # noqa: E731
-    produce(rows, ident)
     full, hdl_f, ptrs_f = symm_buffer("full", (BT * p * Sl, 3 * HpD), qkv, group)
-    # index order (β·t, s, rank, q|k|v): the three runs of one (token, rank) land back to back in the peer's row, so
-    # consecutive threads write 3·Hp·D contiguous elements over NVLink
-    ops.scatter_runs(qkv, ptrs_f, 2, (BT, Sl, p, 3), (Sl * 3 * C, 3 * C, HpD, C),
-                     (p * Sl * 3 * HpD, 3 * HpD, 0, HpD), HpD, dst_base=rank * Sl * 3 * HpD)
+    fused = _fused_scatter(ops, qkv, D, C, p)
+    if fused:
+        # the qkv projection's epilogue stores every head group straight into its owner's [β·T, S, 3, Hp·D] buffer:
+        # GEMM and all-to-all are one kernel, the NVLink writes ride under the MMAs
+        produce(rows, ident, scatter=(ptrs_f, Sl, rank))
+        stats["fused_qkv_scatter"] += 1
+    else:
+        produce(rows, ident)
+        stats["scatter_kernel"] += 1
+        # index order (β·t, s, rank, q|k|v): the three runs of one (token, rank) land back to back in the peer's row,
+        # so consecutive threads write 3·Hp·D contiguous elements over NVLink
+        ops.scatter_runs(qkv, ptrs_f, 2, (BT, Sl, p, 3), (Sl * 3 * C, 3 * C, HpD, C),
+                         (p * Sl * 3 * HpD, 3 * HpD, 0, HpD), HpD, dst_base=rank * Sl * 3 * HpD)
     hdl_f.barrier()
     o = _buf(("o", 0), (BT * p * Sl, HpD), qkv)
-    ops.attention(full[:, :HpD], full[:, HpD:2 * HpD], full[:, 2 * HpD:], o, BT, p * Sl, p * Sl, Hp, D, scale,
-                  kv_map=kv_map)
     ao, hdl_a, ptrs_a = ao_sym
-    ops.scatter_runs(o, ptrs_a, 1, (BT, p, Sl, 1), (p * Sl * HpD, Sl * HpD, HpD, 0), (Sl * C, 0, C, 0), HpD,
-                     dst_base=rank * HpD)
+    if fused and hasattr(ops, "attention_scatter") and ops.attention_scatter_supported(qkv, D, p):
+        # the attention epilogue stores every output row into its owner's [N_l, C] buffer (o: partial sums of the
+        # cross-view K/V sets only)
+        ops.attention_scatter(full[:, :HpD], full[:, HpD:2 * HpD], full[:, 2 * HpD:], o, BT, p * Sl, p * Sl, Hp, D,
+                              scale, ptrs_a, Sl, C, rank * HpD, kv_map=kv_map)
+        stats["fused_out_scatter"] += 1
+    else:
+        ops.attention(full[:, :HpD], full[:, HpD:2 * HpD], full[:, 2 * HpD:], o, BT, p * Sl, p * Sl, Hp, D, scale,
+                      kv_map=kv_map)
+        ops.scatter_runs(o, ptrs_a, 1, (BT, p, Sl, 1), (p * Sl * HpD, Sl * HpD, HpD, 0), (Sl * C, 0, C, 0), HpD,
+                         dst_base=rank * HpD)
     hdl_a.barrier()
     consume(rows, ident)
 

@@ -277,3 +277,58 @@ def test_scatter_runs_matches_all_to_all_layouts():
     for r in range(p):
         ref = torch.stack([o[q].view(BT, p, Sl, HpD)[:, r] for q in range(p)], dim=2)               # [BT, Sl, p, HpD]
         assert torch.equal(ao[r].view(BT, Sl, p, HpD), ref)
+
+
+@pytest.mark.parametrize("p,Hp,D,BT,Sl", [(2, 8, 72, 3, 150), (8, 2, 72, 2, 333), (4, 4, 72, 1, 64), (2, 3, 64, 2, 70)])
+def test_gemm_qkv_scatter_equals_gemm_plus_scatter(p, Hp, D, BT, Sl):
+    """The qkv projection whose epilogue scatters head groups to the "peers" (all on one GPU here) must produce,
+    bit for bit, what the plain projection followed by the scatter kernel produces."""
+    bf = torch.bfloat16
+    HpD, C = Hp * D, p * Hp * D
+    K = 256
+    for rank in (0, p - 1):
+        a = rnd(BT * Sl, K, dtype=bf, seed=3 + rank)
+        w = rnd(3 * C, K, dtype=bf, seed=5) * 0.1
+        bias = rnd(3 * C, dtype=bf, seed=6)
+        wq, wk = rnd(D, dtype=bf, seed=7) + 1.0, rnd(D, dtype=bf, seed=8) + 1.0
+        qkv = torch.empty(BT * Sl, 3 * C, dtype=bf, device=DEV)
+        ops().gemm(a, w, bias, qkv, rms=(wq, wk, D, C, C))
+        want = [torch.zeros(BT * p * Sl, 3 * HpD, dtype=bf, device=DEV) for _ in range(p)]
+        ops().scatter_runs(qkv, [t.data_ptr() for t in want], 2, (BT, Sl, p, 3), (Sl * 3 * C, 3 * C, HpD, C),
+                           (p * Sl * 3 * HpD, 3 * HpD, 0, HpD), HpD, dst_base=rank * Sl * 3 * HpD)
+        got = [torch.zeros(BT * p * Sl, 3 * HpD, dtype=bf, device=DEV) for _ in range(p)]
+        assert ops().gemm_qkv_scatter_supported(a, w, D, p)
+        ops().gemm_qkv_scatter(a, w, bias, (wq, wk, D, C, C), [t.data_ptr() for t in got], Sl, rank)
+        torch.cuda.synchronize()
+        for g in range(p):
+            assert torch.equal(got[g], want[g]), (p, rank, g)
+        assert got[0].view(BT, p, Sl, 3 * HpD)[:, rank].abs().sum() > 0
+
+
+@pytest.mark.parametrize("p,Hp,D,BT,Sl,n_sets", [(2, 4, 72, 3, 150, 1), (8, 2, 72, 2, 40, 2), (4, 2, 64, 2, 100, 1),
+                                                 (2, 2, 72, 4, 333, 2)])
+def test_attention_scatter_equals_attention_plus_scatter(p, Hp, D, BT, Sl, n_sets):
+    """Attention whose epilogue scatters the output rows to the "peers" (all on one GPU here) must produce, bit for
+    bit, what the plain kernel followed by the scatter kernel produces (self and cross-view flavours)."""
+    bf = torch.bfloat16
+    HpD, C, S = Hp * D, p * Hp * D, p * Sl
+    rank = p - 1
+    full = rnd(BT * S, 3 * HpD, dtype=bf, seed=21)
+    kv_map = None
+    if n_sets == 2:
+        kv_map = torch.tensor([[(i + 1) % BT, (i - 1) % BT] for i in range(BT)], dtype=torch.int32, device=DEV)
+    q, k, v = full[:, :HpD], full[:, HpD:2 * HpD], full[:, 2 * HpD:]
+    o = torch.empty(BT * S, HpD, dtype=bf, device=DEV)
+    ops().attention(q, k, v, o, BT, S, S, Hp, D, D ** -0.5, kv_map=kv_map)
+    want = [torch.zeros(BT * Sl, C, dtype=bf, device=DEV) for _ in range(p)]
+    ops().scatter_runs(o, [t.data_ptr() for t in want], 1, (BT, p, Sl, 1), (p * Sl * HpD, Sl * HpD, HpD, 0),
+                       (Sl * C, 0, C, 0), HpD, dst_base=rank * HpD)
+    got = [torch.zeros(BT * Sl, C, dtype=bf, device=DEV) for _ in range(p)]
+    part = torch.empty(BT * S, HpD, dtype=bf, device=DEV)
+    assert ops().attention_scatter_supported(q, D, p)
+    ops().attention_scatter(q, k, v, part, BT, S, S, Hp, D, D ** -0.5, [t.data_ptr() for t in got], Sl, C, rank * HpD,
+                            kv_map=kv_map)
+    torch.cuda.synchronize()
+    for g in range(p):
+        assert torch.equal(got[g], want[g]), (p, g)
+    assert got[0][:, rank * HpD:(rank + 1) * HpD].abs().sum() > 0

@@ -19,7 +19,9 @@ def _free_port():
     return port
 
 
-def _worker(rank, world, port, wl_name, xm, ret, nccl_path):
+def _worker(rank, world, port, wl_name, xm, ret, mode):
+    nccl_path = mode == "nccl"
+    os.environ["MDV2_SP_FUSED"] = "1" if mode == "peer_fused" else "0"
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     for p in (root, os.path.join(root, "tests")):
@@ -48,19 +50,26 @@ def _worker(rank, world, port, wl_name, xm, ret, nccl_path):
             torch.cuda.synchronize()
             ret[(rank, key)] = rel_l2(out.cpu(), fix["out"])
             ret[(rank, "peer")] = getattr(model._ws, "ao_sym", None) is not None
+            ret[(rank, "fused_" + key)] = sp.stats["fused_qkv_scatter"]
+            ret[(rank, "fused_out_" + key)] = sp.stats["fused_out_scatter"]
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("nccl_path", [False, True])
+@pytest.mark.parametrize("mode", ["peer_fused", "peer", "nccl"])
 @pytest.mark.parametrize("wl_name,xm", [("tiny_d72", "first0")])
-def test_sequence_parallel_nccl_world2(wl_name, xm, nccl_path):
+def test_sequence_parallel_nccl_world2(wl_name, xm, mode):
+    """peer_fused: qkv GEMM epilogue scatters into the peers' HBM; peer: separate scatter kernel; nccl: all-to-all."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     world = 2
     ret = mp.Manager().dict()
-    mp.spawn(_worker, args=(world, _free_port(), wl_name, xm, ret, nccl_path), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), wl_name, xm, ret, mode), nprocs=world, join=True)
     for r in range(world):
-        assert ret[(r, "peer")] == (not nccl_path), "wrong exchange path taken"
+        assert ret[(r, "peer")] == (mode != "nccl"), "wrong exchange path taken"
+        # fp32 runs first (SIMT GEMMs: never fused); the bf16 forwards take the fused epilogue in peer_fused mode
+        assert ret[(r, "fused_fp32")] == 0
+        assert (ret[(r, "fused_bf16")] > 0) == (mode == "peer_fused"), "wrong qkv scatter path taken"
+        assert (ret[(r, "fused_out_bf16")] > 0) == (mode == "peer_fused"), "wrong output scatter path taken"
         assert ret[(r, "fp32")] < 1e-4, ret[(r, "fp32")]
         assert ret[(r, "bf16")] < 1e-2, ret[(r, "bf16")]
