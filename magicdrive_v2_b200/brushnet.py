@@ -1,0 +1,131 @@
+"""BrushNet variant of the denoiser: a third stream of ``depth`` control-style blocks fed with
+``[x | shallow-encoded masked video | mask]`` whose per-block ``after_proj`` skips are added to the base stream.
+
+Mirror of ``MagicDriveSTDiT3BrushNet`` and ``ShallowEncoder`` (``magicdrive_stdit3.py:1247-1867``): same constructor
+(config keys ``brushnet_skip_cross_attn``, ``control_skip_cross_view``), same
+``forward(x, x_inpaint, mask_inpaint, timestep, y, maps, bbox, cams, rel_pos, fps, height, width, ...)`` signature,
+same state-dict keys (``shallow_encoder.*``, ``brushnet_blocks_s/t.*``, ``x_brushnet_embedder.*``).  The blocks run on
+the same libmdv2 kernels as the base and control streams; the pixel-space ``ShallowEncoder`` convolutions and the
+trilinear mask resize do not depend on the timestep — they run once per sample on stock torch ops and are cached
+across the sampling steps like the other condition encoders.  LoRA on the base blocks (``use_lora_base_blocks``,
+training-time) and the SDE variant are not built.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .blocks import STDiT3Block
+from .config import MagicDriveSTDiT3Config
+from .registry import MODELS
+from .stdit3 import MagicDriveSTDiT3, PatchEmbedParams, _build
+
+
+class ShallowEncoder(nn.Module):
+    """(β, 3, 4t+1, 8h, 8w) -> (β, out_channels, t, h, w): three stride-2 convs + one conv per frame, then a
+    (5,1,1)/stride-4 temporal conv (magicdrive_stdit3.py:1247-1311)."""
+
+    def __init__(self, in_channels=3, out_channels=4, temporal_downsample=4):
+        super().__init__()
+        self.temporal_downsample = temporal_downsample
+        self.conv1 = nn.Conv2d(in_channels, 64, kernel_size=3, stride=2, padding=1)
+        self.conv2 = nn.Conv2d(64, 128, kernel_size=3, stride=2, padding=1)
+        self.conv3 = nn.Conv2d(128, 256, kernel_size=3, stride=2, padding=1)
+        self.conv4 = nn.Conv2d(256, out_channels, kernel_size=3, stride=1, padding=1)
+        td = temporal_downsample
+        self.temporal_conv = nn.Conv3d(out_channels, out_channels, kernel_size=(td + 1, 1, 1), stride=(td, 1, 1),
+                                       padding=(td // 2, 0, 0))
+
+    def forward(self, x, chunk_size=64):
+        B, _, T, _, _ = x.shape
+        x = x.permute(0, 2, 1, 3, 4).flatten(0, 1)                                   # (β t) c h w
+        chunks = []
+        for i in range(0, x.shape[0], chunk_size):
+            ch = F.relu(self.conv1(x[i:i + chunk_size]))
+            ch = F.relu(self.conv2(ch))
+            ch = F.relu(self.conv3(ch))
+            chunks.append(self.conv4(ch))
+        x = torch.cat(chunks, dim=0)
+        x = x.view(B, T, *x.shape[1:]).permute(0, 2, 1, 3, 4)
+        return self.temporal_conv(x)
+
+
+class MagicDriveSTDiT3BrushNet(MagicDriveSTDiT3):
+    def __init__(self, config: MagicDriveSTDiT3Config):
+        super().__init__(config)
+        c = config
+        if getattr(c, "use_lora_base_blocks", False):
+            raise NotImplementedError("LoRA on the base blocks (training-time) is not part of the inference drop-in")
+        C, NH = self.hidden_size, self.num_heads
+        self.shallow_encoder = ShallowEncoder(3, self.in_channels, temporal_downsample=4)
+        skip_ca = getattr(c, "brushnet_skip_cross_attn", True)
+        self.brushnet_blocks_s = nn.ModuleList([
+            STDiT3Block(C, NH, self.mlp_ratio, qk_norm=c.qk_norm, is_control_block=True, skip_cross_attn=skip_ca,
+                        skip_cross_view=c.control_skip_cross_view) for _ in range(self.depth)])
+        self.brushnet_blocks_t = nn.ModuleList([
+            STDiT3Block(C, NH, self.mlp_ratio, qk_norm=c.qk_norm, temporal=True, is_control_block=True,
+                        skip_cross_attn=skip_ca) for _ in range(self.depth)])
+        self.x_brushnet_embedder = PatchEmbedParams(self.patch_size, self.in_channels * 2 + 1, C)
+        self._inpaint_cache = None
+
+    def _apply(self, fn, *a, **k):
+        self._inpaint_cache = None
+        return super()._apply(fn, *a, **k)
+
+    @torch.no_grad()
+    def _encode_inpaint(self, dtype, x_inpaint, mask_inpaint, NC, thw):
+        """Timestep-independent half of the third stream: -> (encoded video [β, Cin, T, Hx, Wx], mask [β, 1, T, Hx, Wx]).
+        Cached on the identity of the two inputs (the sampler hands the same tensors every step)."""
+        key = self._condition_key([x_inpaint, mask_inpaint, NC, tuple(thw), dtype])
+        if self.cache_conditions and self._inpaint_cache is not None and self._inpaint_cache[0] == key:
+            return self._inpaint_cache[1]
+
+        def views(t):                                       # "B (C NC) T ... -> (B NC) C T ..."
+            B_, CN = t.shape[:2]
+            return t.to(dtype).view(B_, CN // NC, NC, *t.shape[2:]).transpose(1, 2).flatten(0, 1)
+        enc = self.shallow_encoder(views(x_inpaint))
+        mk = F.interpolate(views(mask_inpaint), size=tuple(thw), mode="trilinear", align_corners=False)
+        assert tuple(enc.shape[-3:]) == tuple(thw) == tuple(mk.shape[-3:]), \
+            f"After encoding - x:{tuple(thw)}, x_inpaint_encoded:{tuple(enc.shape)}, mask_inpaint:{tuple(mk.shape)}"
+        out = (enc.contiguous(), mk.contiguous())
+        if self.cache_conditions:
+            self._inpaint_cache = (key, out, (x_inpaint, mask_inpaint))
+        return out
+
+    def _embed_inpaint(self, ops, dtype, x, inpaint, geometry, pos_l):
+        """x_brushnet_embedder(cat[x, enc, mask]) + pos  ->  [N, C] tokens of the third stream
+        (magicdrive_stdit3.py:1648-1654); rows in the canonical (β, t, s) order, local S-slice under SP."""
+        b, NC, T, Tx, Hx, Wx, Hp, Wp, s0, Sl = geometry
+        x_inpaint, mask_inpaint = inpaint
+        enc, mk = self._encode_inpaint(dtype, x_inpaint, mask_inpaint, NC, (Tx, Hx, Wx))
+        xv = x.view(b, self.in_channels, NC, Tx, Hx, Wx).transpose(1, 2).flatten(0, 1)   # (b NC) C T H W
+        # 2·Cin + 1 = 33 channels -> 132 gathered inputs per patch; zero channels pad that to a multiple of 64 so the
+        # embedding runs on the tcgen05 GEMM like the other two streams
+        cin = 2 * self.in_channels + 1
+        cpad = -(-cin * 4 // 64) * 16
+        zeros = torch.zeros(xv.shape[0], cpad - cin, *xv.shape[2:], dtype=dtype, device=x.device)
+        xcat = torch.cat([xv, enc, mk, zeros], dim=1).contiguous()
+        n_rows = b * NC * T * Sl
+        patches = torch.empty(n_rows, cpad * 4, dtype=dtype, device=x.device)
+        ops.patchify(xcat, patches, 1, Hp, Wp, s0, Sl)
+        w = self.x_brushnet_embedder.proj.weight                                      # [C, cin, 1, 2, 2]
+        w2d = F.pad(w.view(w.shape[0], cin, 4), (0, 0, 0, cpad - cin)).reshape(w.shape[0], cpad * 4).contiguous()
+        xi = torch.empty(n_rows, self.hidden_size, dtype=dtype, device=x.device)
+        ops.gemm(patches, w2d, self.x_brushnet_embedder.proj.bias, xi, res=pos_l, res_map=(Sl, 0))
+        return xi
+
+    @torch.no_grad()
+    def forward(self, x, x_inpaint, mask_inpaint, timestep, y, maps, bbox, cams, rel_pos, fps, height, width,
+                drop_cond_mask=None, drop_frame_mask=None, mv_order_map=None, t_order_map=None, mask=None,
+                x_mask=None, **kwargs):
+        return super().forward(x, timestep, y, maps, bbox, cams, rel_pos, fps, height, width,
+                               drop_cond_mask=drop_cond_mask, drop_frame_mask=drop_frame_mask,
+                               mv_order_map=mv_order_map, t_order_map=t_order_map, mask=mask, x_mask=x_mask,
+                               _inpaint=(x_inpaint, mask_inpaint), **kwargs)
+
+
+@MODELS.register_module("MagicDriveSTDiT3-XL/2-BrushNet")
+def MagicDriveSTDiT3_XL_2_BrushNet(from_pretrained=None, force_huggingface=False, **kwargs):
+    """Registry factory with the reference's name and signature (magicdrive_stdit3.py:2573-2595)."""
+    return _build(MagicDriveSTDiT3BrushNet, from_pretrained, force_huggingface, **kwargs)

@@ -99,6 +99,8 @@ class MagicDriveSTDiT3(PreTrainedModel):
 
     config_class = MagicDriveSTDiT3Config
     _ops = None           # ops backend (the sm_100a library binding); tests may inject a spec backend
+    _BLOCK_LISTS = ("base_blocks_s", "base_blocks_t", "control_blocks_s", "control_blocks_t",
+                    "brushnet_blocks_s", "brushnet_blocks_t")     # (the last two: BrushNet variant, brushnet.py)
 
     def __init__(self, config: MagicDriveSTDiT3Config):
         super().__init__(config)
@@ -294,8 +296,8 @@ class MagicDriveSTDiT3(PreTrainedModel):
     def _all_blocks(self):
         """(name, block) for every block that owns a cross_attn, in a fixed order."""
         out = []
-        for name in ("base_blocks_s", "base_blocks_t", "control_blocks_s", "control_blocks_t"):
-            lst = getattr(self, name)
+        for name in self._BLOCK_LISTS:
+            lst = getattr(self, name, None)
             if lst is not None:
                 out += [(f"{name}.{i}", blk) for i, blk in enumerate(lst)]
         return out
@@ -380,6 +382,7 @@ class MagicDriveSTDiT3(PreTrainedModel):
                 drop_cond_mask=None, drop_frame_mask=None, mv_order_map=None, t_order_map=None,
                 mask=None, x_mask=None, **kwargs):
         ops = self.ops
+        inpaint = kwargs.pop("_inpaint", None)             # (x_inpaint, mask_inpaint): BrushNet variant only
         dtype = self.x_embedder.proj.weight.dtype
         dev = x.device
         b, real_T = x.size(0), rel_pos.size(1)
@@ -454,16 +457,22 @@ class MagicDriveSTDiT3(PreTrainedModel):
         xc = torch.empty(N, C, dtype=dtype, device=dev)
         ops.gemm(patches, xe.weight2d(), xe.proj.bias, xc, res=pm, res_map=(T * Sl, NC))
 
+        # third stream (BrushNet): tokens of [x | encoded masked video | mask], one skip per block into xb
+        xi = None
+        if inpaint is not None:
+            xi = self._embed_inpaint(ops, dtype, x, inpaint, (b, NC, T, Tx, Hx, Wx, Hp, Wp, s0, Sl), pos_l)
+
         # --- modulation tables for all blocks at once ---
         tm6 = tm_sel.reshape(b, T, 6, C)
         tm3 = tm_sel[:, :, :3].reshape(b, T, 3, 1)
         mods = {name: self._mod_tables(getattr(self, name), "scale_shift_table", tm6, 6, dtype)
-                for name in ("base_blocks_s", "base_blocks_t", "control_blocks_s", "control_blocks_t")
-                if getattr(self, name) is not None}
+                for name in self._BLOCK_LISTS if getattr(self, name, None) is not None}
         mod_mva = self._mod_tables(self.base_blocks_s, "scale_shift_table_mva", tm3, 3, dtype)
-        mva_ctrl = None
-        if not self.control_blocks_s[0].skip_cross_view:
+        mva_ctrl = mva_brush = None
+        if self.control_depth > 0 and not self.control_blocks_s[0].skip_cross_view:
             mva_ctrl = self._mod_tables(self.control_blocks_s, "scale_shift_table_mva", tm3, 3, dtype)
+        if xi is not None and not self.brushnet_blocks_s[0].skip_cross_view:
+            mva_brush = self._mod_tables(self.brushnet_blocks_s, "scale_shift_table_mva", tm3, 3, dtype)
 
         ctx = _Ctx()
         ctx.L, ctx.y_frames = cnd["L"], cnd["y_frames"]
@@ -481,12 +490,19 @@ class MagicDriveSTDiT3(PreTrainedModel):
                 self.control_blocks_s[i].run(ops, xc, ws, d, mods["control_blocks_s"][i],
                                              None if mva_ctrl is None else mva_ctrl[i],
                                              ykv.get(f"control_blocks_s.{i}"), ctx, skip_into=xb)
+            if xi is not None:                             # magicdrive_stdit3.py:1714-1728 / :1790-1804
+                self.brushnet_blocks_s[i].run(ops, xi, ws, d, mods["brushnet_blocks_s"][i],
+                                              None if mva_brush is None else mva_brush[i],
+                                              ykv.get(f"brushnet_blocks_s.{i}"), ctx, skip_into=xb)
             if self.base_blocks_t is not None:
                 self.base_blocks_t[i].run(ops, xb, ws, d, mods["base_blocks_t"][i], None,
                                           ykv.get(f"base_blocks_t.{i}"), ctx)
             if i < self.control_depth and self.control_blocks_t is not None:
                 self.control_blocks_t[i].run(ops, xc, ws, d, mods["control_blocks_t"][i], None,
                                              ykv.get(f"control_blocks_t.{i}"), ctx, skip_into=xb)
+            if xi is not None and self.base_blocks_t is not None and self.brushnet_blocks_t is not None:
+                self.brushnet_blocks_t[i].run(ops, xi, ws, d, mods["brushnet_blocks_t"][i], None,
+                                              ykv.get(f"brushnet_blocks_t.{i}"), ctx, skip_into=xb)
 
         # --- final layer (blocks.py:893-905) + unpatchify (P7) ---
         fl = self.final_layer

@@ -85,6 +85,18 @@ def latent_frames(t_pix: int) -> int:
     return 1 if t_pix == 1 else (t_pix - 1) // 4 + 1
 
 
+def make_inpaint_inputs(workload: dict, seed: int = 0, kw: dict | None = None):
+    """Extra inputs of the BrushNet variant (magicdrive_stdit3.py:1466-1487): the masked pixel video of every view,
+    ``x_inpaint [b, 3·NC, Tpix, Hpix, Wpix]``, and its binary mask ``mask_inpaint [b, NC, Tpix, Hpix, Wpix]``."""
+    g = torch.Generator().manual_seed(seed + 77)
+    b, NC, t_pix = workload["b"], workload["NC"], workload["t_pix"]
+    H, W = math.ceil(workload["height"] / 8) * 8, math.ceil(workload["width"] / 8) * 8
+    mask = (torch.rand(b, NC, t_pix, H // 8, W // 8, generator=g) > 0.3).float()
+    mask = mask.repeat_interleave(8, dim=3).repeat_interleave(8, dim=4)
+    x_inpaint = torch.randn(b, 3 * NC, t_pix, H, W, generator=g) * mask.repeat(1, 3, 1, 1, 1)
+    return dict(x_inpaint=x_inpaint, mask_inpaint=mask)
+
+
 def make_inputs(workload: dict, seed: int = 0, x_mask: str | None = "ones", kw: dict | None = None):
     """Synthetic forward kwargs (CPU tensors, fp32).  ``x_mask``: None | "ones" | "first0"."""
     kw = kw or model_kwargs(**workload["model"])

@@ -355,12 +355,26 @@ def patch_embed(p, x):                                       # blocks.py:132-155
     return F.conv3d(x, p["proj.weight"], p["proj.bias"], stride=(1, 2, 2)).flatten(2).transpose(1, 2)
 
 
+def shallow_encoder(p, x, chunk_size=64):                    # ShallowEncoder.forward, stdit3.py:1284-1311
+    B_NC, _, T, _, _ = x.shape
+    x = rearrange(x, "b c t h w -> (b t) c h w")
+    chunks = []
+    for i in range(0, x.shape[0], chunk_size):
+        ch = x[i:i + chunk_size]
+        ch = F.relu(conv(p, "conv1", ch, stride=2, padding=1))
+        ch = F.relu(conv(p, "conv2", ch, stride=2, padding=1))
+        ch = F.relu(conv(p, "conv3", ch, stride=2, padding=1))
+        chunks.append(conv(p, "conv4", ch, stride=1, padding=1))
+    x = rearrange(torch.cat(chunks, dim=0), "(b t) c h w -> b c t h w", b=B_NC, t=T)
+    return F.conv3d(x, p["temporal_conv.weight"], p["temporal_conv.bias"], stride=(4, 1, 1), padding=(2, 0, 0))
+
+
 # ---------------------------------------------------------------------------------------------
-# the denoiser forward, stdit3.py:1021-1218
+# the denoiser forward, stdit3.py:1021-1218 (BrushNet variant with x_inpaint / mask_inpaint: :1466-1867)
 # ---------------------------------------------------------------------------------------------
 @torch.no_grad()
 def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, width, mv_order_map=None,
-            mask=None, x_mask=None, max_layers=None, timers=None, **_):
+            mask=None, x_mask=None, max_layers=None, timers=None, x_inpaint=None, mask_inpaint=None, **_):
     """sd: state dict (fp32 tensors); cfg: constructor kwargs (synth.model_kwargs).
     ``max_layers`` truncates the block stack; ``timers`` collects wall time per block kind (bench.py)."""
     p = P(sd)
@@ -377,6 +391,13 @@ def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, wid
     NC = len(mv_order_map)
     x = rearrange(x.to(dtype), "B (C NC) T ... -> (B NC) C T ...", NC=NC)
     timestep, y = timestep.to(dtype), y.to(dtype)
+    enc = mi = None
+    if x_inpaint is not None:                                # stdit3.py:1504-1524
+        xi = rearrange(x_inpaint.to(dtype), "B (C NC) T ... -> (B NC) C T ...", NC=NC)
+        mi = rearrange(mask_inpaint.to(dtype), "B (C NC) T ... -> (B NC) C T ...", NC=NC)
+        enc = shallow_encoder(p.sub("shallow_encoder"), xi)
+        mi = F.interpolate(mi, size=x.shape[-3:], mode="trilinear", align_corners=False)
+        assert x.shape[-3:] == enc.shape[-3:] == mi.shape[-3:]
     _, _, Tx, Hx, Wx = x.size()
     x_in_shape = x.shape
     T, H, W = Tx, -(-Hx // 2), -(-Wx // 2)
@@ -387,6 +408,8 @@ def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, wid
         h_pad = q - H % q
     if h_pad > 0:
         x = F.pad(x, (0, 0, 0, h_pad * 2))
+        if enc is not None:                                  # stdit3.py:1586-1587
+            enc, mi = F.pad(enc, (0, 0, 0, h_pad * 2)), F.pad(mi, (0, 0, 0, h_pad * 2))
         H += h_pad
         S = H * W
     base_size = round(S ** 0.5)
@@ -429,6 +452,10 @@ def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, wid
     xe = "x_control_embedder" if p.has("x_control_embedder.proj.weight") else "x_embedder"
     x_c = rearrange(patch_embed(p.sub(xe), x), "B (T S) C -> B T S C", T=T, S=S) + pos
     c = x_c + linear(p, "before_proj", c)
+    x_inp = None
+    if enc is not None:                                      # stdit3.py:1648-1654
+        x_inp = patch_embed(p.sub("x_brushnet_embedder"), torch.cat([x, enc, mi], dim=1))
+        x_inp = rearrange(rearrange(x_inp, "B (T S) C -> B T S C", T=T, S=S) + pos, "B T S C -> B (T S) C")
     x = rearrange(x_b, "B T S C -> B (T S) C")
     c = rearrange(c, "B T S C -> B (T S) C")
     if x_mask is not None:
@@ -445,16 +472,25 @@ def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, wid
         if timers is not None:                               # bench.py: wall seconds per block kind
             timers[name] = timers.get(name, 0.0) + time.perf_counter() - t_
         return r
-    for i in range(depth):                                   # stdit3.py:1173-1198
+    has_bt = p.has("brushnet_blocks_t.0.attn.qkv.weight")
+    for i in range(depth):                                   # stdit3.py:1173-1198 / BrushNet :1684-1850
         x = blk("base_blocks_s", i, x, False)
+        skip = 0
         if i < cdepth:
             c, skip = blk("control_blocks_s", i, c, False)
+        if x_inp is not None:
+            x_inp, skip_i = blk("brushnet_blocks_s", i, x_inp, False)
+            x = x + skip + skip_i if i < cdepth else x + skip_i
+        elif i < cdepth:
             x = x + skip
         if has_t:
             x = blk("base_blocks_t", i, x, True)
         if i < cdepth and has_ct:
             c, skip = blk("control_blocks_t", i, c, True)
             x = x + skip
+        if x_inp is not None and has_bt and has_t:
+            x_inp, skip_i = blk("brushnet_blocks_t", i, x_inp, True)
+            x = x + skip_i
 
     # final layer incl. its t0 quirk (blocks.py:893-905): x_zero is built from the modulated x
     fl = p.sub("final_layer")

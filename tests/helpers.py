@@ -102,3 +102,21 @@ class cpu_randn_like:
 
     def __call__(self, x):
         return torch.randn(x.shape, generator=self.gen, dtype=x.dtype).to(x.device)
+
+
+def build_brushnet(workload_name, skip_cross_attn=True, seed=0, **extra_kw):
+    from magicdrive_v2_b200.brushnet import MagicDriveSTDiT3BrushNet
+    wl = synth.WORKLOADS[workload_name]
+    kw = synth.model_kwargs(**wl["model"])
+    kw["brushnet_skip_cross_attn"] = skip_cross_attn
+    kw.update(extra_kw)
+    torch.manual_seed(0)
+    model = MagicDriveSTDiT3BrushNet(MagicDriveSTDiT3Config(**kw)).eval()
+    synth.fill_params(model, seed=seed)
+    return model, wl, kw
+
+
+def brushnet_inputs(wl, kw, fix):
+    inp = synth.make_inputs(wl, seed=fix["seed"], x_mask=fix["x_mask"], kw=kw)
+    inp.update(synth.make_inpaint_inputs(wl, seed=fix["seed"], kw=kw))
+    return inp

@@ -48,3 +48,24 @@ def test_native_library_is_the_path_that_runs():
     model(**inp)
     assert ops.launches - before > 50            # every hot-path step is a libmdv2 launch
     assert type(model).__mro__[0].__name__ == "MagicDriveSTDiT3" and type(model)._ops is ops
+
+
+BRUSH_CASES = [("brushnet_tiny_9f_first0_noca.pt", True), ("brushnet_tiny_9f_None_ca.pt", False)]
+
+
+@pytest.mark.parametrize("fixture,skip_ca", BRUSH_CASES)
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2)])
+def test_brushnet_matches_reference(fixture, skip_ca, dtype, tol):
+    """BrushNet variant (third stream of control-style blocks, magicdrive_stdit3.py:1314-1867) through libmdv2
+    against the output of the REAL reference module."""
+    from helpers import brushnet_inputs, build_brushnet
+    fix = load_golden(fixture)
+    model, wl, kw = build_brushnet(fix["workload"], skip_ca)
+    model = model.to("cuda", dtype)
+    inp = synth.to_device(brushnet_inputs(wl, kw, fix), "cuda")
+    out = model(**inp)
+    torch.cuda.synchronize()
+    assert out.dtype == torch.float32 and out.shape == fix["out"].shape and torch.isfinite(out).all()
+    err = rel_l2(out.cpu(), fix["out"])
+    print(f"brushnet {fixture} {dtype}: rel L2 {err:.3e} (reference's own bf16 gap {fix['ref_bf16_rel_l2']:.3e})")
+    assert err < tol
