@@ -36,6 +36,13 @@ class Dims:
         return self.B * self.T * self.S
 
 
+def W(lin):
+    """Effective weight of a Linear holder: the LoRA-folded copy when the BrushNet variant attached one
+    (brushnet.py, magicdrive_stdit3.py:1422-1464), else the parameter itself."""
+    w = getattr(lin, "_w_eff", None)
+    return lin.weight if w is None else w
+
+
 class Workspace:
     """Scratch activations shared by all blocks of one forward (allocated once per shape)."""
 
@@ -102,12 +109,12 @@ class STDiT3Block(nn.Module):
         def qkv_rows(rows, tab, scatter=None):
             ops.ln_modulate(x[rows], ws.xm[rows], tab(mod), 0, 1, geo)
             if scatter is not None:                     # sequence parallel: the epilogue stores into the peers' HBM
-                ops.gemm_qkv_scatter(ws.xm[rows], a.qkv.weight, a.qkv.bias, (qn, kn, D, C, C), *scatter)
+                ops.gemm_qkv_scatter(ws.xm[rows], W(a.qkv), a.qkv.bias, (qn, kn, D, C, C), *scatter)
             else:
-                ops.gemm(ws.xm[rows], a.qkv.weight, a.qkv.bias, ws.qkv[rows], geo=geo, rms=(qn, kn, D, C, C))
+                ops.gemm(ws.xm[rows], W(a.qkv), a.qkv.bias, ws.qkv[rows], geo=geo, rms=(qn, kn, D, C, C))
 
         def proj_rows(rows, tab):
-            ops.gemm(ws.ao[rows], a.proj.weight, a.proj.bias, x[rows], geo=geo, gate=(tab(mod), 2), res=x[rows])
+            ops.gemm(ws.ao[rows], W(a.proj), a.proj.bias, x[rows], geo=geo, gate=(tab(mod), 2), res=x[rows])
 
         if self.temporal:
             rows = slice(0, x.shape[0])
@@ -120,13 +127,13 @@ class STDiT3Block(nn.Module):
         # (e) cross-attention onto the condition tokens: un-normed, un-gated
         if not self.skip_cross_attn:
             ca = self.cross_attn
-            ops.gemm(x, ca.q_linear.weight, ca.q_linear.bias, ws.xm, geo=geo)
+            ops.gemm(x, W(ca.q_linear), ca.q_linear.bias, ws.xm, geo=geo)
             yk, yv = y_kv[:, :C], y_kv[:, C:]
             if ctx.y_frames == 1:
                 ops.attention(ws.xm, yk, yv, ws.ao, d.B, T * S, ctx.L, H, D, scale)
             else:
                 ops.attention(ws.xm, yk, yv, ws.ao, d.B * T, S, ctx.L, H, D, scale)
-            ops.gemm(ws.ao, ca.proj.weight, ca.proj.bias, x, geo=geo, res=x)
+            ops.gemm(ws.ao, W(ca.proj), ca.proj.bias, x, geo=geo, res=x)
 
         # (f) cross-view attention (spatial base blocks): each view attends to its neighbours
         if not self.skip_cross_view:
@@ -151,8 +158,8 @@ class STDiT3Block(nn.Module):
 
         # (g) MLP
         ops.ln_modulate(x, ws.xm, mod, 3, 4, geo)
-        ops.gemm(ws.xm, self.mlp.fc1.weight, self.mlp.fc1.bias, ws.hid, geo=geo, act="gelu")
-        ops.gemm(ws.hid, self.mlp.fc2.weight, self.mlp.fc2.bias, x, geo=geo, gate=(mod, 5), res=x)
+        ops.gemm(ws.xm, W(self.mlp.fc1), self.mlp.fc1.bias, ws.hid, geo=geo, act="gelu")
+        ops.gemm(ws.hid, W(self.mlp.fc2), self.mlp.fc2.bias, x, geo=geo, gate=(mod, 5), res=x)
 
         # (h) control skip: x_base += after_proj(x_control)
         if self.is_control_block and skip_into is not None:

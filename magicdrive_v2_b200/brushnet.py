@@ -7,10 +7,14 @@ Mirror of ``MagicDriveSTDiT3BrushNet`` and ``ShallowEncoder`` (``magicdrive_stdi
 same state-dict keys (``shallow_encoder.*``, ``brushnet_blocks_s/t.*``, ``x_brushnet_embedder.*``).  The blocks run on
 the same libmdv2 kernels as the base and control streams; the pixel-space ``ShallowEncoder`` convolutions and the
 trilinear mask resize do not depend on the timestep — they run once per sample on stock torch ops and are cached
-across the sampling steps like the other condition encoders.  LoRA on the base blocks (``use_lora_base_blocks``,
-training-time) and the SDE variant are not built.
+across the sampling steps like the other condition encoders.  LoRA adapters on the base blocks
+(``use_lora_base_blocks``, ``:1422-1464``) keep their ``lora_A`` / ``lora_B`` state-dict entries and are folded into
+the projection weights once per load (``W + α/r · B·A``), so the hot path runs the same GEMMs.  The SDE variant is not
+built.
 """
 from __future__ import annotations
+
+import math
 
 import torch
 import torch.nn as nn
@@ -20,6 +24,21 @@ from .blocks import STDiT3Block
 from .config import MagicDriveSTDiT3Config
 from .registry import MODELS
 from .stdit3 import MagicDriveSTDiT3, PatchEmbedParams, _build
+
+
+_LORA_TARGETS = (("attn", ("qkv", "proj")), ("cross_attn", ("q_linear", "kv_linear", "proj")), ("mlp", ("fc1", "fc2")))
+
+
+def _add_lora(lin: nn.Linear, rank: int, alpha: float) -> nn.Linear:
+    """``_add_lora_to_linear`` (magicdrive_stdit3.py:1422-1464): ``lora_A [r, in]`` (kaiming), ``lora_B [out, r]``
+    (zeros) registered on the Linear itself, so the keys are ``….qkv.lora_A`` / ``….qkv.lora_B``."""
+    lin.lora_A = nn.Parameter(torch.zeros(rank, lin.in_features))
+    lin.lora_B = nn.Parameter(torch.zeros(lin.out_features, rank))
+    nn.init.kaiming_uniform_(lin.lora_A, a=math.sqrt(5))
+    lin.lora_scaling = alpha / rank
+    lin._w_eff = None
+    lin._w_key = None
+    return lin
 
 
 class ShallowEncoder(nn.Module):
@@ -55,8 +74,8 @@ class MagicDriveSTDiT3BrushNet(MagicDriveSTDiT3):
     def __init__(self, config: MagicDriveSTDiT3Config):
         super().__init__(config)
         c = config
-        if getattr(c, "use_lora_base_blocks", False):
-            raise NotImplementedError("LoRA on the base blocks (training-time) is not part of the inference drop-in")
+        if getattr(c, "lora_dropout", 0.0):
+            raise NotImplementedError("LoRA dropout is a training-time feature; the inference drop-in folds the adapters")
         C, NH = self.hidden_size, self.num_heads
         self.shallow_encoder = ShallowEncoder(3, self.in_channels, temporal_downsample=4)
         skip_ca = getattr(c, "brushnet_skip_cross_attn", True)
@@ -68,10 +87,45 @@ class MagicDriveSTDiT3BrushNet(MagicDriveSTDiT3):
                         skip_cross_attn=skip_ca) for _ in range(self.depth)])
         self.x_brushnet_embedder = PatchEmbedParams(self.patch_size, self.in_channels * 2 + 1, C)
         self._inpaint_cache = None
+        self._lora = []
+        if getattr(c, "use_lora_base_blocks", False):       # magicdrive_stdit3.py:1374-1378, :1398-1420
+            for lst in (self.base_blocks_s, self.base_blocks_t):
+                for blk in (lst if lst is not None else []):
+                    for sub, names in _LORA_TARGETS:
+                        for n in names:
+                            lin = getattr(getattr(blk, sub, None), n, None)
+                            if isinstance(lin, nn.Linear):
+                                _add_lora(lin, c.lora_rank, c.lora_alpha)
+                                # reference quirk, replicated: the spatial MultiHeadAttention applies its qkv with
+                                # F.linear on weight slices (blocks.py:438-445), which by-passes the patched forward —
+                                # those adapters exist in the state dict but never act
+                                if not (sub == "attn" and n == "qkv" and not blk.temporal):
+                                    self._lora.append(lin)
+
+    def _drop_folded(self):
+        for lin in self._lora:
+            lin._w_eff = None
+            lin._w_key = None
 
     def _apply(self, fn, *a, **k):
         self._inpaint_cache = None
+        self._drop_folded()
         return super()._apply(fn, *a, **k)
+
+    def load_state_dict(self, *a, **k):
+        self._drop_folded()
+        return super().load_state_dict(*a, **k)
+
+    @torch.no_grad()
+    def _fold_lora(self):
+        """W_eff = W + (alpha / rank) · B·A, in fp32, rounded once to the model dtype; refreshed when a parameter
+        was written since the last fold."""
+        for lin in self._lora:
+            key = tuple((t.data_ptr(), t._version) for t in (lin.weight, lin.lora_A, lin.lora_B))
+            if lin._w_eff is None or lin._w_key != key:
+                w = lin.weight.float() + lin.lora_scaling * (lin.lora_B.float() @ lin.lora_A.float())
+                lin._w_eff, lin._w_key = w.to(lin.weight.dtype).contiguous(), key
+                self._cond_cache = None                     # cached cross-attention K/V used the old kv_linear
 
     @torch.no_grad()
     def _encode_inpaint(self, dtype, x_inpaint, mask_inpaint, NC, thw):
@@ -119,6 +173,7 @@ class MagicDriveSTDiT3BrushNet(MagicDriveSTDiT3):
     def forward(self, x, x_inpaint, mask_inpaint, timestep, y, maps, bbox, cams, rel_pos, fps, height, width,
                 drop_cond_mask=None, drop_frame_mask=None, mv_order_map=None, t_order_map=None, mask=None,
                 x_mask=None, **kwargs):
+        self._fold_lora()
         return super().forward(x, timestep, y, maps, bbox, cams, rel_pos, fps, height, width,
                                drop_cond_mask=drop_cond_mask, drop_frame_mask=drop_frame_mask,
                                mv_order_map=mv_order_map, t_order_map=t_order_map, mask=mask, x_mask=x_mask,

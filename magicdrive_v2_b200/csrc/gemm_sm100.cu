@@ -429,7 +429,12 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tw, const Params& p, cudaSt
     configured = true;
   }
   const int64_t tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * (p.N / BN);
-  const int64_t pairs = mdv2_num_sms() / 2;
+  int64_t pairs = mdv2_num_sms() / 2;
+  static const int forced_pairs = [] {                 // tuning hook (tools/gemm_pairs_probe.py)
+    const char* e = getenv("MDV2_GEMM_PAIRS");
+    return e ? atoi(e) : 0;
+  }();
+  if (forced_pairs > 0 && forced_pairs < pairs) pairs = forced_pairs;
   const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
   gemm_sm100_kernel<BN, HD><<<grid, NUM_THREADS, C::SMEM, st>>>(ta, tw, p);
   MDV2_CHECK_LAUNCH("gemm_sm100");

@@ -21,7 +21,7 @@ import torch.nn.functional as F
 from transformers import PreTrainedModel
 
 from . import indexmaps
-from .blocks import Dims, STDiT3Block, Workspace
+from .blocks import Dims, STDiT3Block, Workspace, W
 from .config import MagicDriveSTDiT3Config
 from .embedders import (CaptionEmbedder, MapControlTempEmbedding, RotaryFreqs, SizeEmbedder,
                         TimestepEmbedder, resolve_embedder)
@@ -348,7 +348,7 @@ class MagicDriveSTDiT3(PreTrainedModel):
         for name, blk in self._all_blocks():
             if not blk.skip_cross_attn:
                 kv = torch.empty(cond2d.shape[0], 2 * C, dtype=dtype, device=cond.device)
-                ops.gemm(cond2d, blk.cross_attn.kv_linear.weight, blk.cross_attn.kv_linear.bias, kv)
+                ops.gemm(cond2d, W(blk.cross_attn.kv_linear), blk.cross_attn.kv_linear.bias, kv)
                 y_kv[name] = kv
         # map tokens: patchify -> patchifier GEMM -> before_proj GEMM   (rows: b, T, S)
         S = Hp * Wp

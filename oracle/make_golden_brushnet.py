@@ -13,28 +13,31 @@ sys.path.insert(0, ROOT)
 from magicdrive_v2_b200 import synth  # noqa: E402
 from oracle import ref_loader  # noqa: E402
 
-# (workload, x_mask, brushnet_skip_cross_attn)
-CASES = [("tiny_9f", "first0", True), ("tiny_9f", None, False)]
+# (workload, x_mask, brushnet_skip_cross_attn, use_lora_base_blocks)
+CASES = [("tiny_9f", "first0", True, False), ("tiny_9f", None, False, False), ("tiny_9f", "ones", True, True)]
 
 
 def main():
-    for wl_name, xm, skip_ca in CASES:
+    for wl_name, xm, skip_ca, lora in CASES:
         wl = synth.WORKLOADS[wl_name]
         kw = synth.model_kwargs(**wl["model"])
         kw["brushnet_skip_cross_attn"] = skip_ca
+        if lora:
+            kw.update(use_lora_base_blocks=True, lora_rank=8, lora_alpha=4)
         torch.manual_seed(0)
         ref = synth.fill_params(ref_loader.build_reference_model(kw, brushnet=True).eval(), seed=0)
         inp = synth.make_inputs(wl, seed=0, x_mask=xm, kw=kw)
         inp.update(synth.make_inpaint_inputs(wl, seed=0, kw=kw))
         with torch.no_grad():
             out = ref(**inp)
-            ref_bf = copy.deepcopy(ref).to(torch.bfloat16)
+            sd = {k: v.clone() for k, v in ref.state_dict().items()}
+            # (the LoRA forward closures capture the original Linear objects: cast in place instead of deep-copying)
+            ref_bf = ref.to(torch.bfloat16) if lora else copy.deepcopy(ref).to(torch.bfloat16)
             out_bf = ref_bf(**synth.to_device(inp, "cpu", torch.bfloat16))
-        sd = ref.state_dict()
-        fix = dict(workload=wl_name, x_mask=xm, seed=0, brushnet_skip_cross_attn=skip_ca, out=out.clone(),
+        fix = dict(workload=wl_name, x_mask=xm, seed=0, brushnet_skip_cross_attn=skip_ca, lora=lora, out=out.clone(),
                    ref_bf16_rel_l2=((out_bf - out).norm() / out.norm()).item(),
                    state_shapes={k: tuple(v.shape) for k, v in sd.items()} if skip_ca else None)
-        name = f"brushnet_{wl_name}_{xm}_{'noca' if skip_ca else 'ca'}.pt"
+        name = f"brushnet_{wl_name}_{xm}_{'noca' if skip_ca else 'ca'}{'_lora' if lora else ''}.pt"
         torch.save(fix, os.path.join(ROOT, "tests", "golden", name))
         print(name, tuple(out.shape), "mean|v|", out.abs().mean().item(), "ref bf16 gap", fix["ref_bf16_rel_l2"])
 

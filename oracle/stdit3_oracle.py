@@ -37,8 +37,14 @@ class P:
         return self.sd.get(self.prefix + k)
 
 
+LORA_SCALING = 2.0          # lora_alpha / lora_rank of the BrushNet variant (set by forward from cfg)
+
+
 def linear(p, name, x):
-    return F.linear(x, p[name + ".weight"], p.get(name + ".bias"))
+    r = F.linear(x, p[name + ".weight"], p.get(name + ".bias"))
+    if p.has(name + ".lora_A"):                       # lora_forward, stdit3.py:1452-1462
+        r = r + ((x @ p[name + ".lora_A"].T) @ p[name + ".lora_B"].T) * LORA_SCALING
+    return r
 
 
 def layernorm(x):                                   # blocks.py:71-80 (eps 1e-6, no affine)
@@ -377,6 +383,8 @@ def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, wid
             mask=None, x_mask=None, max_layers=None, timers=None, x_inpaint=None, mask_inpaint=None, **_):
     """sd: state dict (fp32 tensors); cfg: constructor kwargs (synth.model_kwargs).
     ``max_layers`` truncates the block stack; ``timers`` collects wall time per block kind (bench.py)."""
+    global LORA_SCALING
+    LORA_SCALING = cfg.get("lora_alpha", 32) / cfg.get("lora_rank", 16)
     p = P(sd)
     C, NH = cfg["hidden_size"], cfg["num_heads"]
     depth, cdepth = cfg["depth"], cfg["control_depth"]

@@ -116,6 +116,9 @@ def build_brushnet(workload_name, skip_cross_attn=True, seed=0, **extra_kw):
     return model, wl, kw
 
 
+LORA_KW = dict(use_lora_base_blocks=True, lora_rank=8, lora_alpha=4)      # as oracle/make_golden_brushnet.py
+
+
 def brushnet_inputs(wl, kw, fix):
     inp = synth.make_inputs(wl, seed=fix["seed"], x_mask=fix["x_mask"], kw=kw)
     inp.update(synth.make_inpaint_inputs(wl, seed=fix["seed"], kw=kw))

@@ -50,7 +50,8 @@ def test_native_library_is_the_path_that_runs():
     assert type(model).__mro__[0].__name__ == "MagicDriveSTDiT3" and type(model)._ops is ops
 
 
-BRUSH_CASES = [("brushnet_tiny_9f_first0_noca.pt", True), ("brushnet_tiny_9f_None_ca.pt", False)]
+BRUSH_CASES = [("brushnet_tiny_9f_first0_noca.pt", True), ("brushnet_tiny_9f_None_ca.pt", False),
+               ("brushnet_tiny_9f_ones_noca_lora.pt", True)]
 
 
 @pytest.mark.parametrize("fixture,skip_ca", BRUSH_CASES)
@@ -58,9 +59,9 @@ BRUSH_CASES = [("brushnet_tiny_9f_first0_noca.pt", True), ("brushnet_tiny_9f_Non
 def test_brushnet_matches_reference(fixture, skip_ca, dtype, tol):
     """BrushNet variant (third stream of control-style blocks, magicdrive_stdit3.py:1314-1867) through libmdv2
     against the output of the REAL reference module."""
-    from helpers import brushnet_inputs, build_brushnet
+    from helpers import LORA_KW, brushnet_inputs, build_brushnet
     fix = load_golden(fixture)
-    model, wl, kw = build_brushnet(fix["workload"], skip_ca)
+    model, wl, kw = build_brushnet(fix["workload"], skip_ca, **(LORA_KW if fix.get("lora") else {}))
     model = model.to("cuda", dtype)
     inp = synth.to_device(brushnet_inputs(wl, kw, fix), "cuda")
     out = model(**inp)

@@ -20,25 +20,28 @@ def test_oracle_matches_reference_golden(wl_name, xm):
     assert rel_l2(out, fix["out"]) < 2e-5
 
 
-BRUSH_CASES = [("tiny_9f", "first0", True), ("tiny_9f", None, False)]
+BRUSH_CASES = [("tiny_9f", "first0", True, False), ("tiny_9f", None, False, False), ("tiny_9f", "ones", True, True)]
 
 
-def _brush(wl_name, skip_ca):
+def _brush(wl_name, skip_ca, lora=False):
     from magicdrive_v2_b200.brushnet import MagicDriveSTDiT3BrushNet
     from magicdrive_v2_b200.config import MagicDriveSTDiT3Config
     wl = synth.WORKLOADS[wl_name]
     kw = synth.model_kwargs(**wl["model"])
     kw["brushnet_skip_cross_attn"] = skip_ca
+    if lora:
+        kw.update(use_lora_base_blocks=True, lora_rank=8, lora_alpha=4)
     torch.manual_seed(0)
     model = synth.fill_params(MagicDriveSTDiT3BrushNet(MagicDriveSTDiT3Config(**kw)).eval(), seed=0)
     return model, wl, kw
 
 
-@pytest.mark.parametrize("wl_name,xm,skip_ca", BRUSH_CASES)
-def test_brushnet_oracle_matches_reference_golden(wl_name, xm, skip_ca):
-    """BrushNet variant (magicdrive_stdit3.py:1314-1867): oracle vs the output of the REAL reference."""
-    fix = load_golden(f"brushnet_{wl_name}_{xm}_{'noca' if skip_ca else 'ca'}.pt")
-    model, wl, kw = _brush(wl_name, skip_ca)
+@pytest.mark.parametrize("wl_name,xm,skip_ca,lora", BRUSH_CASES)
+def test_brushnet_oracle_matches_reference_golden(wl_name, xm, skip_ca, lora):
+    """BrushNet variant (magicdrive_stdit3.py:1314-1867, with and without LoRA adapters on the base blocks): oracle
+    vs the output of the REAL reference."""
+    fix = load_golden(f"brushnet_{wl_name}_{xm}_{'noca' if skip_ca else 'ca'}{'_lora' if lora else ''}.pt")
+    model, wl, kw = _brush(wl_name, skip_ca, lora)
     sd = {k: v.clone() for k, v in model.state_dict().items()}
     if fix["state_shapes"] is not None:              # same key set and shapes as the reference module
         assert {k: tuple(v.shape) for k, v in sd.items()} == fix["state_shapes"]
