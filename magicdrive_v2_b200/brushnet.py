@@ -9,8 +9,11 @@ the same libmdv2 kernels as the base and control streams; the pixel-space ``Shal
 trilinear mask resize do not depend on the timestep — they run once per sample on stock torch ops and are cached
 across the sampling steps like the other condition encoders.  LoRA adapters on the base blocks
 (``use_lora_base_blocks``, ``:1422-1464``) keep their ``lora_A`` / ``lora_B`` state-dict entries and are folded into
-the projection weights once per load (``W + α/r · B·A``), so the hot path runs the same GEMMs.  The SDE variant is not
-built.
+the projection weights once per load (``W + α/r · B·A``), so the hot path runs the same GEMMs.
+
+``MagicDriveSTDiT3SDEBrushNet`` (``magicdrive_stdit3.py:1870-2470``) gives the third stream its own noise level: the
+shallow-encoded video is mixed with a noise latent at ``timestep_inpaint`` (``add_noise``, ``:1976-1994``) and the
+brushnet blocks are modulated by ``t_combine_block(cat[t_block(t), t_inpaint_block(t_inpaint)])`` (``:2215-2232``).
 """
 from __future__ import annotations
 
@@ -147,12 +150,14 @@ class MagicDriveSTDiT3BrushNet(MagicDriveSTDiT3):
             self._inpaint_cache = (key, out, (x_inpaint, mask_inpaint))
         return out
 
-    def _embed_inpaint(self, ops, dtype, x, inpaint, geometry, pos_l):
+    def _embed_inpaint(self, ops, dtype, x, inpaint, geometry, pos_l, sde=None):
         """x_brushnet_embedder(cat[x, enc, mask]) + pos  ->  [N, C] tokens of the third stream
         (magicdrive_stdit3.py:1648-1654); rows in the canonical (β, t, s) order, local S-slice under SP."""
         b, NC, T, Tx, Hx, Wx, Hp, Wp, s0, Sl = geometry
         x_inpaint, mask_inpaint = inpaint
         enc, mk = self._encode_inpaint(dtype, x_inpaint, mask_inpaint, NC, (Tx, Hx, Wx))
+        if sde is not None:
+            enc = self._noise_inpaint(dtype, enc, NC, *sde)
         xv = x.view(b, self.in_channels, NC, Tx, Hx, Wx).transpose(1, 2).flatten(0, 1)   # (b NC) C T H W
         # 2·Cin + 1 = 33 channels -> 132 gathered inputs per patch; zero channels pad that to a multiple of 64 so the
         # embedding runs on the tcgen05 GEMM like the other two streams
@@ -180,7 +185,70 @@ class MagicDriveSTDiT3BrushNet(MagicDriveSTDiT3):
                                _inpaint=(x_inpaint, mask_inpaint), **kwargs)
 
 
+class MagicDriveSTDiT3SDEBrushNet(MagicDriveSTDiT3BrushNet):
+    """BrushNet whose inpaint branch runs at an independent timestep (magicdrive_stdit3.py:1870-2470).  Same modules as
+    the BrushNet variant plus ``t_inpaint_block`` and ``t_combine_block``; forward takes ``timestep_inpaint``,
+    ``num_timesteps`` and ``noise_inpaint_encoded`` (``:1996-2020``)."""
+
+    def __init__(self, config: MagicDriveSTDiT3Config):
+        super().__init__(config)
+        C = self.hidden_size
+        self.t_inpaint_block = nn.Sequential(nn.SiLU(), nn.Linear(C, 6 * C, bias=True))
+        self.t_combine_block = nn.Sequential(nn.SiLU(), nn.Linear(12 * C, 6 * C, bias=True))
+
+    @staticmethod
+    def add_noise(original_samples, noise, timesteps, num_timesteps):
+        """``timepoint·x + (1 - timepoint)·noise`` with ``timepoint = 1 - t / num_timesteps`` per sample, in fp32
+        (magicdrive_stdit3.py:1976-1994)."""
+        tp = 1 - timesteps.float() / num_timesteps
+        tp = tp.view(-1, 1, 1, 1, 1)
+        return tp * original_samples + (1 - tp) * noise
+
+    def _noise_inpaint(self, dtype, enc, NC, timestep_inpaint, num_timesteps, noise):
+        """Noised encoding of the masked video (magicdrive_stdit3.py:2099-2111); the clean encoding stays cached, the
+        mix depends on ``timestep_inpaint`` and is redone every step."""
+        if noise is None:
+            # the reference draws phase-preserving "structured" noise on the CPU with the un-vendored
+            # ``structured_noise`` package (:2057-2096); its arithmetic is not on this box, so the caller supplies it
+            raise NotImplementedError("noise_inpaint_encoded=None needs the third-party structured_noise package; "
+                                      "pass noise_inpaint_encoded [b, C·NC, T, h, w]")
+        B_, CN = noise.shape[:2]
+        nz = noise.to(dtype).view(B_, CN // NC, NC, *noise.shape[2:]).transpose(1, 2).flatten(0, 1)
+        assert nz.shape == enc.shape, \
+            f"noise_inpaint_encoded shape {tuple(nz.shape)} does not match x_inpaint_encoded shape {tuple(enc.shape)}!"
+        ts = timestep_inpaint.to(enc.device).repeat_interleave(NC, dim=0)
+        return self.add_noise(enc, nz, ts, num_timesteps).to(dtype).contiguous()
+
+    def _sde_time_vectors(self, timestep_inpaint, dtype, fps_e, t_mlp, t0, t0_mlp):
+        """-> (t_combined_mlp, t0_combined_mlp | None), each [b, 6C] (magicdrive_stdit3.py:2215-2232).  Unlike
+        ``timestep``, ``timestep_inpaint`` is NOT rounded to the model dtype before the sinusoid (reference quirk)."""
+        t_in = self.t_embedder(timestep_inpaint.to(fps_e.device), dtype=dtype) + fps_e
+        tc = self.t_combine_block(torch.cat([t_mlp, self.t_inpaint_block(t_in)], dim=-1))
+        tc0 = None
+        if t0 is not None:
+            tc0 = self.t_combine_block(torch.cat([t0_mlp, self.t_inpaint_block(t0)], dim=-1))
+        return tc, tc0
+
+    @torch.no_grad()
+    def forward(self, x, x_inpaint, mask_inpaint, timestep, timestep_inpaint, num_timesteps, y, maps, bbox, cams,
+                rel_pos, fps, height, width, noise_inpaint_encoded=None, drop_cond_mask=None, drop_frame_mask=None,
+                mv_order_map=None, t_order_map=None, mask=None, x_mask=None, **kwargs):
+        self._fold_lora()
+        return MagicDriveSTDiT3.forward(
+            self, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, width, drop_cond_mask=drop_cond_mask,
+            drop_frame_mask=drop_frame_mask, mv_order_map=mv_order_map, t_order_map=t_order_map, mask=mask,
+            x_mask=x_mask, _inpaint=(x_inpaint, mask_inpaint),
+            _sde=(timestep_inpaint, num_timesteps, noise_inpaint_encoded), **kwargs)
+
+
 @MODELS.register_module("MagicDriveSTDiT3-XL/2-BrushNet")
 def MagicDriveSTDiT3_XL_2_BrushNet(from_pretrained=None, force_huggingface=False, **kwargs):
-    """Registry factory with the reference's name and signature (magicdrive_stdit3.py:2573-2595)."""
-    return _build(MagicDriveSTDiT3BrushNet, from_pretrained, force_huggingface, **kwargs)
+    """Registry factory with the reference's name and signature (magicdrive_stdit3.py:2573-2595); like the reference
+    it loads non-strictly, so a base-model checkpoint initialises the shared streams."""
+    return _build(MagicDriveSTDiT3BrushNet, from_pretrained, force_huggingface, strict=False, **kwargs)
+
+
+@MODELS.register_module("MagicDriveSTDiT3-XL/2-SDEBrushNet")
+def MagicDriveSTDiT3_XL_2_SDEBrushNet(from_pretrained=None, force_huggingface=False, **kwargs):
+    """Registry factory with the reference's name and signature (magicdrive_stdit3.py:2598-2620)."""
+    return _build(MagicDriveSTDiT3SDEBrushNet, from_pretrained, force_huggingface, strict=False, **kwargs)

@@ -383,6 +383,7 @@ class MagicDriveSTDiT3(PreTrainedModel):
                 mask=None, x_mask=None, **kwargs):
         ops = self.ops
         inpaint = kwargs.pop("_inpaint", None)             # (x_inpaint, mask_inpaint): BrushNet variant only
+        sde = kwargs.pop("_sde", None)                     # (timestep_inpaint, num_timesteps, noise): SDE variant only
         dtype = self.x_embedder.proj.weight.dtype
         dev = x.device
         b, real_T = x.size(0), rel_pos.size(1)
@@ -426,8 +427,13 @@ class MagicDriveSTDiT3(PreTrainedModel):
             sel = x_mask.to(dev).bool()[:, :, None]                                    # [b, T, 1]
             tm_sel = torch.where(sel, t_mlp[:, None], t0_mlp[:, None])                 # [b, T, 6C]
         else:
-            t0 = None
+            t0 = t0_mlp = None
             tm_sel = t_mlp[:, None].expand(b, T, 6 * C)
+        tm_sel_brush = tm_sel
+        if sde is not None:                                # the third stream is modulated by its own time vector
+            tc, tc0 = self._sde_time_vectors(sde[0], dtype, fps_e, t_mlp, t0, t0_mlp)
+            tm_sel_brush = (torch.where(sel, tc[:, None], tc0[:, None]) if x_mask is not None
+                            else tc[:, None].expand(b, T, 6 * C))
 
         # --- conditions (cached) ---
         geom = (b, NC, T, Hp, Wp, h_pad, (Tx, Hx, Wx))
@@ -460,19 +466,22 @@ class MagicDriveSTDiT3(PreTrainedModel):
         # third stream (BrushNet): tokens of [x | encoded masked video | mask], one skip per block into xb
         xi = None
         if inpaint is not None:
-            xi = self._embed_inpaint(ops, dtype, x, inpaint, (b, NC, T, Tx, Hx, Wx, Hp, Wp, s0, Sl), pos_l)
+            xi = self._embed_inpaint(ops, dtype, x, inpaint, (b, NC, T, Tx, Hx, Wx, Hp, Wp, s0, Sl), pos_l, sde)
 
         # --- modulation tables for all blocks at once ---
         tm6 = tm_sel.reshape(b, T, 6, C)
         tm3 = tm_sel[:, :, :3].reshape(b, T, 3, 1)
-        mods = {name: self._mod_tables(getattr(self, name), "scale_shift_table", tm6, 6, dtype)
+        tm6b = tm_sel_brush.reshape(b, T, 6, C)
+        mods = {name: self._mod_tables(getattr(self, name), "scale_shift_table",
+                                       tm6b if name.startswith("brushnet") else tm6, 6, dtype)
                 for name in self._BLOCK_LISTS if getattr(self, name, None) is not None}
         mod_mva = self._mod_tables(self.base_blocks_s, "scale_shift_table_mva", tm3, 3, dtype)
         mva_ctrl = mva_brush = None
         if self.control_depth > 0 and not self.control_blocks_s[0].skip_cross_view:
             mva_ctrl = self._mod_tables(self.control_blocks_s, "scale_shift_table_mva", tm3, 3, dtype)
         if xi is not None and not self.brushnet_blocks_s[0].skip_cross_view:
-            mva_brush = self._mod_tables(self.brushnet_blocks_s, "scale_shift_table_mva", tm3, 3, dtype)
+            mva_brush = self._mod_tables(self.brushnet_blocks_s, "scale_shift_table_mva",
+                                         tm_sel_brush[:, :, :3].reshape(b, T, 3, 1), 3, dtype)
 
         ctx = _Ctx()
         ctx.L, ctx.y_frames = cnd["L"], cnd["y_frames"]
@@ -567,7 +576,7 @@ class MagicDriveSTDiT3(PreTrainedModel):
         return sp.gather_tokens(yo, d, p, group)
 
 
-def _build(cls, from_pretrained=None, force_huggingface=False, **kwargs):
+def _build(cls, from_pretrained=None, force_huggingface=False, strict=True, **kwargs):
     if from_pretrained is not None and not os.path.exists(from_pretrained):
         return cls.from_pretrained(from_pretrained, **kwargs)
     kwargs.pop("from_pretrained_pixart", None)
@@ -575,7 +584,7 @@ def _build(cls, from_pretrained=None, force_huggingface=False, **kwargs):
     model = cls(config)
     if from_pretrained is not None:
         from .checkpoint import load_checkpoint
-        load_checkpoint(model, from_pretrained, strict=True)
+        load_checkpoint(model, from_pretrained, strict=strict)
     else:
         logger.info("Your model does not use any pre-trained model.")
     return model

@@ -97,6 +97,19 @@ def make_inpaint_inputs(workload: dict, seed: int = 0, kw: dict | None = None):
     return dict(x_inpaint=x_inpaint, mask_inpaint=mask)
 
 
+def make_sde_inputs(workload: dict, seed: int = 0, kw: dict | None = None):
+    """Extra inputs of the SDE-BrushNet variant (magicdrive_stdit3.py:1996-2020): the inpaint branch's own timestep
+    ``timestep_inpaint [b]``, the schedule length ``num_timesteps`` and the noise latent mixed into the encoded video,
+    ``noise_inpaint_encoded [b, Cin·NC, T, h, w]`` (same packing as ``x``)."""
+    kw = kw or model_kwargs(**workload["model"])
+    g = torch.Generator().manual_seed(seed + 78)
+    b, NC = workload["b"], workload["NC"]
+    T = latent_frames(workload["t_pix"])
+    h, w = math.ceil(workload["height"] / 8), math.ceil(workload["width"] / 8)
+    noise = torch.randn(b, kw["in_channels"] * NC, T, h, w, generator=g)
+    return dict(timestep_inpaint=torch.full((b,), 300.0), num_timesteps=1000, noise_inpaint_encoded=noise)
+
+
 def make_inputs(workload: dict, seed: int = 0, x_mask: str | None = "ones", kw: dict | None = None):
     """Synthetic forward kwargs (CPU tensors, fp32).  ``x_mask``: None | "ones" | "first0"."""
     kw = kw or model_kwargs(**workload["model"])

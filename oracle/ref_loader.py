@@ -50,11 +50,13 @@ def load_reference():
     return importlib.import_module(name)
 
 
-def build_reference_model(kwargs: dict, brushnet: bool = False):
-    """Builds the reference nn.Module from constructor kwargs (see synth.model_kwargs)."""
+def build_reference_model(kwargs: dict, brushnet=False):
+    """Builds the reference nn.Module from constructor kwargs (see synth.model_kwargs).  ``brushnet``: False | True |
+    "sde" (the SDE-BrushNet class, magicdrive_stdit3.py:1870)."""
     ref = load_reference()
     cfg = ref.MagicDriveSTDiT3Config(**kwargs)
-    cls = ref.MagicDriveSTDiT3BrushNet if brushnet else ref.MagicDriveSTDiT3
+    cls = (ref.MagicDriveSTDiT3SDEBrushNet if brushnet == "sde" else
+           ref.MagicDriveSTDiT3BrushNet if brushnet else ref.MagicDriveSTDiT3)
     return cls(cfg)
 
 

@@ -380,7 +380,8 @@ def shallow_encoder(p, x, chunk_size=64):                    # ShallowEncoder.fo
 # ---------------------------------------------------------------------------------------------
 @torch.no_grad()
 def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, width, mv_order_map=None,
-            mask=None, x_mask=None, max_layers=None, timers=None, x_inpaint=None, mask_inpaint=None, **_):
+            mask=None, x_mask=None, max_layers=None, timers=None, x_inpaint=None, mask_inpaint=None,
+            timestep_inpaint=None, num_timesteps=None, noise_inpaint_encoded=None, **_):
     """sd: state dict (fp32 tensors); cfg: constructor kwargs (synth.model_kwargs).
     ``max_layers`` truncates the block stack; ``timers`` collects wall time per block kind (bench.py)."""
     global LORA_SCALING
@@ -404,6 +405,12 @@ def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, wid
         xi = rearrange(x_inpaint.to(dtype), "B (C NC) T ... -> (B NC) C T ...", NC=NC)
         mi = rearrange(mask_inpaint.to(dtype), "B (C NC) T ... -> (B NC) C T ...", NC=NC)
         enc = shallow_encoder(p.sub("shallow_encoder"), xi)
+        if timestep_inpaint is not None:                     # SDE variant: add_noise, stdit3.py:1976-1994, :2099-2111
+            nz = rearrange(noise_inpaint_encoded.to(dtype), "B (C NC) T ... -> (B NC) C T ...", NC=NC)
+            assert nz.shape == enc.shape
+            tp = 1 - repeat(timestep_inpaint, "b -> (b NC)", NC=NC).float() / num_timesteps
+            tp = tp[:, None, None, None, None].repeat(1, *nz.shape[1:])
+            enc = (tp * enc + (1 - tp) * nz).to(dtype)
         mi = F.interpolate(mi, size=x.shape[-3:], mode="trilinear", align_corners=False)
         assert x.shape[-3:] == enc.shape[-3:] == mi.shape[-3:]
     _, _, Tx, Hx, Wx = x.size()
@@ -431,6 +438,15 @@ def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, wid
     if x_mask is not None:
         t0 = t_embed(p.sub("t_embedder"), torch.zeros_like(timestep), dtype) + fps_e
         t0_mlp = linear(p, "t_block.1", F.silu(t0))
+
+    tb_mlp, tb0_mlp = t_mlp, t0_mlp                          # time vectors of the brushnet blocks
+    if timestep_inpaint is not None:                         # SDE variant, stdit3.py:2215-2232
+        t_in = t_embed(p.sub("t_embedder"), timestep_inpaint, dtype) + fps_e
+        tb_mlp = linear(p, "t_combine_block.1",
+                        F.silu(torch.cat([t_mlp, linear(p, "t_inpaint_block.1", F.silu(t_in))], dim=-1)))
+        if x_mask is not None:
+            tb0_mlp = linear(p, "t_combine_block.1",
+                             F.silu(torch.cat([t0_mlp, linear(p, "t_inpaint_block.1", F.silu(t0))], dim=-1)))
 
     # condition sequence, stdit3.py:918-961
     yt = mlp(p.sub("y_embedder.y_proj"), y)                   # [B,1,L,C]
@@ -475,8 +491,10 @@ def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, wid
     def blk(name, i, h, temporal):
         import time
         t_ = time.perf_counter()
-        r = block_forward(p.sub(f"{name}.{i}"), h, cond, t_mlp, x_mask, t0_mlp, T, S, NC, mv_order_map, NH,
-                          temporal, freqs if temporal else None)
+        brush = name.startswith("brushnet")
+        r = block_forward(p.sub(f"{name}.{i}"), h, cond, tb_mlp if brush else t_mlp, x_mask,
+                          tb0_mlp if brush else t0_mlp, T, S, NC, mv_order_map, NH, temporal,
+                          freqs if temporal else None)
         if timers is not None:                               # bench.py: wall seconds per block kind
             timers[name] = timers.get(name, 0.0) + time.perf_counter() - t_
         return r

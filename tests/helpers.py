@@ -104,8 +104,9 @@ class cpu_randn_like:
         return torch.randn(x.shape, generator=self.gen, dtype=x.dtype).to(x.device)
 
 
-def build_brushnet(workload_name, skip_cross_attn=True, seed=0, **extra_kw):
-    from magicdrive_v2_b200.brushnet import MagicDriveSTDiT3BrushNet
+def build_brushnet(workload_name, skip_cross_attn=True, seed=0, sde=False, **extra_kw):
+    from magicdrive_v2_b200 import brushnet
+    MagicDriveSTDiT3BrushNet = brushnet.MagicDriveSTDiT3SDEBrushNet if sde else brushnet.MagicDriveSTDiT3BrushNet
     wl = synth.WORKLOADS[workload_name]
     kw = synth.model_kwargs(**wl["model"])
     kw["brushnet_skip_cross_attn"] = skip_cross_attn
@@ -122,4 +123,13 @@ LORA_KW = dict(use_lora_base_blocks=True, lora_rank=8, lora_alpha=4)      # as o
 def brushnet_inputs(wl, kw, fix):
     inp = synth.make_inputs(wl, seed=fix["seed"], x_mask=fix["x_mask"], kw=kw)
     inp.update(synth.make_inpaint_inputs(wl, seed=fix["seed"], kw=kw))
+    return inp
+
+
+SDE_CASES = [("sde_tiny_9f_first0_noca.pt", True), ("sde_tiny_9f_None_ca.pt", False)]   # oracle/make_golden_sde.py
+
+
+def sde_inputs(wl, kw, fix):
+    inp = brushnet_inputs(wl, kw, fix)
+    inp.update(synth.make_sde_inputs(wl, seed=fix["seed"], kw=kw))
     return inp

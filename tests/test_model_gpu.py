@@ -70,3 +70,20 @@ def test_brushnet_matches_reference(fixture, skip_ca, dtype, tol):
     err = rel_l2(out.cpu(), fix["out"])
     print(f"brushnet {fixture} {dtype}: rel L2 {err:.3e} (reference's own bf16 gap {fix['ref_bf16_rel_l2']:.3e})")
     assert err < tol
+
+
+@pytest.mark.parametrize("fixture,skip_ca", [("sde_tiny_9f_first0_noca.pt", True), ("sde_tiny_9f_None_ca.pt", False)])
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2)])
+def test_sde_brushnet_matches_reference(fixture, skip_ca, dtype, tol):
+    """SDE-BrushNet variant (magicdrive_stdit3.py:1870-2470) through libmdv2 against the REAL reference module."""
+    from helpers import build_brushnet, sde_inputs
+    fix = load_golden(fixture)
+    model, wl, kw = build_brushnet(fix["workload"], skip_ca, sde=True)
+    model = model.to("cuda", dtype)
+    inp = synth.to_device(sde_inputs(wl, kw, fix), "cuda")
+    out = model(**inp)
+    torch.cuda.synchronize()
+    assert out.dtype == torch.float32 and out.shape == fix["out"].shape and torch.isfinite(out).all()
+    err = rel_l2(out.cpu(), fix["out"])
+    print(f"sde {fixture} {dtype}: rel L2 {err:.3e} (reference's own bf16 gap {fix['ref_bf16_rel_l2']:.3e})")
+    assert err < tol

@@ -50,3 +50,18 @@ def test_brushnet_oracle_matches_reference_golden(wl_name, xm, skip_ca, lora):
     out = stdit3_oracle.forward(sd, kw, **inp)
     assert out.shape == fix["out"].shape
     assert rel_l2(out, fix["out"]) < 2e-5
+
+
+@pytest.mark.parametrize("fixture,skip_ca", [("sde_tiny_9f_first0_noca.pt", True), ("sde_tiny_9f_None_ca.pt", False)])
+def test_sde_brushnet_oracle_matches_reference_golden(fixture, skip_ca):
+    """SDE-BrushNet variant (magicdrive_stdit3.py:1870-2470: noised inpaint encoding at its own timestep, brushnet
+    blocks modulated by t_combine_block): oracle vs the output of the REAL reference, same state-dict layout."""
+    from helpers import build_brushnet, sde_inputs
+    fix = load_golden(fixture)
+    model, wl, kw = build_brushnet(fix["workload"], skip_ca, sde=True)
+    sd = {k: v.clone() for k, v in model.state_dict().items()}
+    if fix["state_shapes"] is not None:
+        assert {k: tuple(v.shape) for k, v in sd.items()} == fix["state_shapes"]
+    out = stdit3_oracle.forward(sd, kw, **sde_inputs(wl, kw, fix))
+    assert out.shape == fix["out"].shape
+    assert rel_l2(out, fix["out"]) < 2e-5
