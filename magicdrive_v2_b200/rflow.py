@@ -93,6 +93,13 @@ class RFLOW:
     @torch.no_grad()
     def sample(self, model, text_encoder, z, prompts, device, neg_prompts=None, additional_args=None, mask=None,
                guidance_scale=None, progress=True):
+        return self._sample(model, text_encoder, z, prompts, device, neg_prompts, additional_args, mask,
+                            guidance_scale, progress, lambda z_in, t2, z, args: model(z_in, t2, **args))
+
+    def _sample(self, model, text_encoder, z, prompts, device, neg_prompts, additional_args, mask, guidance_scale,
+                progress, call):
+        """The sampling loop shared by the three samplers; ``call(z_in, t2, z, model_args)`` is the denoiser call of
+        one step (doubled latent in the model dtype, doubled timestep, the fp32 latent, the doubled conditions)."""
         from . import ops                                           # raises without libmdv2.so: no eager fallback
         if guidance_scale is None:
             guidance_scale = self.cfg_scale
@@ -149,7 +156,7 @@ class RFLOW:
                 noise_added = keep
                 z_in[: z.shape[0]].copy_(z)
                 z_in[z.shape[0]:].copy_(z)
-            pred = model(z_in, t2[i], **model_args)
+            pred = call(z_in, t2[i], z, model_args)
             if pred.shape[1] == z_in.shape[1] * 2:
                 pred = pred.chunk(2, dim=1)[0]
             else:
@@ -158,3 +165,48 @@ class RFLOW:
             z = ops.cfg_euler_step(pred, z, dts[i], guidance_scale, x0=x0, keep=keep,
                                    z_in=None if mask is not None else z_in)
         return z
+
+
+def _doubled(t):
+    return torch.cat([t, t], 0)
+
+
+@SCHEDULERS.register_module("rflow-brushnet")
+class RFLOW_BRUSHNET(RFLOW):
+    """``RFLOW_BRUSHNET`` (rf/__init__.py:121-238): the same loop around the BrushNet denoiser, which also takes the
+    masked pixel video and its mask.  The reference concatenates ``[z_inpaint, z_inpaint]`` / ``[mask, mask]`` anew every
+    step (``:217-218``); here they are doubled ONCE, so the denoiser's identity-keyed inpaint cache (shallow encoder +
+    mask resize) hits on every step after the first."""
+
+    @torch.no_grad()
+    def sample(self, model, text_encoder, z, z_inpaint, mask_inpaint, prompts, device, neg_prompts=None,
+               additional_args=None, mask=None, guidance_scale=None, progress=True):
+        zi, mi = _doubled(z_inpaint), _doubled(mask_inpaint)
+        return self._sample(model, text_encoder, z, prompts, device, neg_prompts, additional_args, mask,
+                            guidance_scale, progress, lambda z_in, t2, z, args: model(z_in, zi, mi, t2, **args))
+
+
+@SCHEDULERS.register_module("rflow-sdebrushnet")
+class RFLOW_SDEBRUSHNET(RFLOW):
+    """``RFLOW_SDEBRUSHNET`` (rf/__init__.py:264-397): the inpaint branch is noised at the fixed level
+    ``inpaint_noise_scale`` with a fresh ``randn_like(z)`` every step (``:362-363``)."""
+
+    def __init__(self, num_sampling_steps=10, num_timesteps=1000, cfg_scale=4.0, use_discrete_timesteps=False,
+                 use_timestep_transform=False, inpaint_noise_scale=0.0, **kwargs):
+        super().__init__(num_sampling_steps, num_timesteps, cfg_scale, use_discrete_timesteps,
+                         use_timestep_transform, **kwargs)
+        self.inpaint_noise_scale = inpaint_noise_scale
+
+    @torch.no_grad()
+    def sample(self, model, text_encoder, z, z_inpaint, mask_inpaint, prompts, device, neg_prompts=None,
+               additional_args=None, mask=None, guidance_scale=None, inpaint_noise_scale=None, progress=True):
+        if inpaint_noise_scale is None:
+            inpaint_noise_scale = self.inpaint_noise_scale
+        zi, mi = _doubled(z_inpaint), _doubled(mask_inpaint)
+        t_in = torch.tensor([inpaint_noise_scale * self.num_timesteps] * (2 * z.shape[0]), device=device)
+
+        def call(z_in, t2, z, args):
+            noise = torch.randn_like(z)
+            return model(z_in, zi, mi, t2, t_in, self.num_timesteps, noise_inpaint_encoded=_doubled(noise), **args)
+        return self._sample(model, text_encoder, z, prompts, device, neg_prompts, additional_args, mask,
+                            guidance_scale, progress, call)

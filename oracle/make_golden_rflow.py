@@ -26,6 +26,21 @@ def main():
                                additional_args=dict(extra), mask=mask, guidance_scale=g, progress=False)
         torch.save(dict(case=name, out=out.clone()), os.path.join(ROOT, "tests", "golden", f"rflow_{name}.pt"))
         print(name, tuple(out.shape), out.dtype, out.float().abs().mean().item())
+    for kind, name in helpers.RFLOW_BRUSH_CASES:        # RFLOW_BRUSHNET / RFLOW_SDEBRUSHNET, rf/__init__.py:121-397
+        kw, z, extra, mask, g = helpers.rflow_inputs(name)
+        dt = z.dtype if z.dtype == torch.bfloat16 else torch.float32
+        zi, mi = helpers.rflow_inpaint_inputs(z)
+        if kind == "brushnet":
+            sched, model = rf.RFLOW_BRUSHNET(**kw), helpers.ToyBrushDenoiser(dt)
+        else:
+            sched = rf.RFLOW_SDEBRUSHNET(inpaint_noise_scale=helpers.SDE_NOISE_SCALE, **kw)
+            model = helpers.ToySDEDenoiser(dt)
+        with mock.patch.object(torch, "randn_like", helpers.cpu_randn_like()):
+            out = sched.sample(model, helpers.ToyTextEncoder(), z.clone(), zi, mi, ["a", "b"][: z.shape[0]], "cpu",
+                               additional_args=dict(extra), mask=mask, guidance_scale=g, progress=False)
+        torch.save(dict(case=name, kind=kind, out=out.clone()),
+                   os.path.join(ROOT, "tests", "golden", f"rflow_{kind}_{name}.pt"))
+        print(kind, name, tuple(out.shape), out.dtype, out.float().abs().mean().item())
 
 
 if __name__ == "__main__":

@@ -23,8 +23,11 @@ def timestep_transform(t, height, width, num_frames, num_timesteps, cog_style, b
 
 
 def sample(model, model_args, z, num_sampling_steps, num_timesteps=1000, guidance_scale=4.0,
-           use_timestep_transform=False, cog_style=False, mask=None, randn_like=torch.randn_like):
-    """model_args already holds the doubled (cond | null) conditions; returns the final latent."""
+           use_timestep_transform=False, cog_style=False, mask=None, randn_like=torch.randn_like, inpaint=None,
+           inpaint_noise_scale=None):
+    """model_args already holds the doubled (cond | null) conditions; returns the final latent.
+    ``inpaint=(z_inpaint, mask_inpaint)`` selects ``RFLOW_BRUSHNET.sample`` (rf/__init__.py:146-238);
+    ``inpaint_noise_scale`` on top of it ``RFLOW_SDEBRUSHNET.sample`` (:291-397)."""
     model_args = dict(model_args)
     n = z.shape[0]
     ts = [torch.tensor([(1.0 - i / num_sampling_steps) * num_timesteps] * n) for i in range(num_sampling_steps)]  # :66-69
@@ -42,7 +45,17 @@ def sample(model, model_args, z, num_sampling_steps, num_timesteps=1000, guidanc
             model_args["x_mask"] = upper.repeat(2, 1)
             z = torch.where((upper & ~noise_added)[:, None, :, None, None], x_noise, x0)
             noise_added = upper
-        pred = model(torch.cat([z, z], 0), torch.cat([t, t], 0), **model_args)                                     # :95-97
+        if inpaint is None:
+            pred = model(torch.cat([z, z], 0), torch.cat([t, t], 0), **model_args)                                 # :95-97
+        else:
+            zi, mi = (torch.cat([a, a], 0) for a in inpaint)                                                       # :217-218
+            if inpaint_noise_scale is None:
+                pred = model(torch.cat([z, z], 0), zi, mi, torch.cat([t, t], 0), **model_args)                     # :219
+            else:
+                t_in = torch.tensor([inpaint_noise_scale * num_timesteps] * n)                                     # :362-363
+                nz = randn_like(z)
+                pred = model(torch.cat([z, z], 0), zi, mi, torch.cat([t, t], 0), torch.cat([t_in, t_in], 0),
+                             num_timesteps, noise_inpaint_encoded=torch.cat([nz, nz], 0), **model_args)            # :372
         pc, pu = pred.chunk(2, dim=0)
         v = pu + guidance_scale * (pc - pu)                                                                        # :101
         dt = (ts[i] - ts[i + 1] if i < len(ts) - 1 else ts[i]) / num_timesteps                                     # :104-105

@@ -64,6 +64,37 @@ class ToyDenoiser(torch.nn.Module):
         return out
 
 
+class ToyBrushDenoiser(ToyDenoiser):
+    """Same exact-arithmetic stand-in with the BrushNet call signature (magicdrive_stdit3.py:1466-1487)."""
+
+    def forward(self, x, x_inpaint, mask_inpaint, timestep, y, x_mask=None, **kwargs):
+        out = ToyDenoiser.forward(self, x, timestep, y, x_mask=x_mask)
+        return out + x_inpaint.float() * mask_inpaint.float() * 0.5
+
+
+class ToySDEDenoiser(ToyDenoiser):
+    """... and with the SDE-BrushNet call signature (magicdrive_stdit3.py:1996-2020)."""
+
+    def forward(self, x, x_inpaint, mask_inpaint, timestep, timestep_inpaint, num_timesteps, y,
+                noise_inpaint_encoded=None, x_mask=None, **kwargs):
+        out = ToyDenoiser.forward(self, x, timestep, y, x_mask=x_mask)
+        out = out + x_inpaint.float() * mask_inpaint.float() * 0.5
+        lvl = (timestep_inpaint.float() * (1.0 / 1024)).view(-1, 1, 1, 1, 1) * (num_timesteps * (1.0 / 1024))
+        return out + noise_inpaint_encoded.float() * lvl
+
+
+def rflow_inpaint_inputs(z):
+    """(z_inpaint, mask_inpaint) for the toy BrushNet samplers: latent-shaped so the toy can add them elementwise."""
+    gen = torch.Generator().manual_seed(13)
+    zi = torch.randn(z.shape, generator=gen).to(z.device)
+    mi = (torch.rand((z.shape[0], 1) + tuple(z.shape[2:]), generator=gen) > 0.4).float().to(z.device)
+    return zi, mi
+
+
+RFLOW_BRUSH_CASES = [("brushnet", "plain"), ("brushnet", "masked"), ("sde", "cog_bf16"), ("sde", "masked")]
+SDE_NOISE_SCALE = 0.375
+
+
 class ToyTextEncoder:
     def encode(self, prompts):
         return dict(y=torch.tensor([0.5 + 0.25 * i for i in range(len(prompts))]))

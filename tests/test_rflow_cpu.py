@@ -25,6 +25,32 @@ def test_oracle_matches_reference_golden(name):
     assert out.dtype == fix["out"].dtype and torch.equal(out, fix["out"])       # bit-exact
 
 
+@pytest.mark.parametrize("kind,name", helpers.RFLOW_BRUSH_CASES)
+def test_brushnet_sampler_oracle_matches_reference_golden(kind, name):
+    """RFLOW_BRUSHNET / RFLOW_SDEBRUSHNET restatement vs latents of the REAL reference samplers (bit-exact)."""
+    kw, z, extra, mask, g = helpers.rflow_inputs(name)
+    fix = helpers.load_golden(f"rflow_{kind}_{name}.pt")
+    dt = z.dtype if z.dtype == torch.bfloat16 else torch.float32
+    model = helpers.ToyBrushDenoiser(dt) if kind == "brushnet" else helpers.ToySDEDenoiser(dt)
+    enc = helpers.ToyTextEncoder()
+    n = z.shape[0]
+    args = dict(y=torch.cat([enc.encode(["a", "b"][:n])["y"], enc.null(n)], 0), **extra)
+    out = rflow_oracle.sample(model, args, z.clone(), kw["num_sampling_steps"],
+                              guidance_scale=g if g is not None else kw["cfg_scale"],
+                              use_timestep_transform=kw.get("use_timestep_transform", False),
+                              cog_style=kw.get("cog_style_trans", False), mask=mask,
+                              randn_like=helpers.cpu_randn_like(), inpaint=helpers.rflow_inpaint_inputs(z),
+                              inpaint_noise_scale=helpers.SDE_NOISE_SCALE if kind == "sde" else None)
+    assert out.dtype == fix["out"].dtype and torch.equal(out, fix["out"])
+
+
+def test_brushnet_samplers_registered():
+    a = SCHEDULERS.build(dict(type="rflow-brushnet", num_sampling_steps=3))
+    b = SCHEDULERS.build(dict(type="rflow-sdebrushnet", num_sampling_steps=3, inpaint_noise_scale=0.25))
+    assert isinstance(a, rflow.RFLOW_BRUSHNET) and isinstance(b, rflow.RFLOW_SDEBRUSHNET)
+    assert b.inpaint_noise_scale == 0.25 and b.num_sampling_steps == 3
+
+
 @pytest.mark.parametrize("name", list(helpers.RFLOW_CASES))
 def test_schedule_matches_oracle(name):
     kw, z, extra, mask, g = helpers.rflow_inputs(name)
@@ -59,3 +85,41 @@ def test_add_noise_matches_reference_formula():
     t = torch.tensor([250.0, 1000.0])
     tp = (1 - t / 1000)[:, None, None, None, None]
     assert torch.equal(s.add_noise(x, nz, t), tp * x + (1 - tp) * nz)
+
+
+def _spec_cfg_euler_step(pred, z, dt, g, x0=None, keep=None, z_in=None):
+    """Eager specification of mdv2_cfg_euler_step (the op sequence of rf/__init__.py:100-109 + the next cat/cast)."""
+    pc, pu = pred.chunk(2, dim=0)
+    out = z + (pu + g * (pc - pu)) * dt[:, None, None, None, None]
+    if keep is not None:
+        out = torch.where(keep.bool()[:, None, :, None, None], out, x0)
+    if z_in is not None:
+        z_in.copy_(torch.cat([out, out], 0))
+    return out.float()
+
+
+@pytest.mark.parametrize("kind,name", [("base", n) for n in helpers.RFLOW_CASES] + helpers.RFLOW_BRUSH_CASES)
+def test_sampler_host_logic_matches_reference_golden(kind, name, monkeypatch):
+    """The three samplers' host logic (schedule upload, mask bookkeeping, doubled inputs, RNG draw order, denoiser call
+    signatures) with the fused step replaced by its eager specification: bit-exact vs the REAL reference latents."""
+    from magicdrive_v2_b200 import ops
+    monkeypatch.setattr(ops, "cfg_euler_step", _spec_cfg_euler_step)
+    monkeypatch.setattr(torch, "randn_like", helpers.cpu_randn_like())
+    kw, z, extra, mask, g = helpers.rflow_inputs(name)
+    dt = z.dtype if z.dtype == torch.bfloat16 else torch.float32
+    prompts = ["a", "b"][: z.shape[0]]
+    common = dict(additional_args=dict(extra), mask=mask, guidance_scale=g, progress=False)
+    if kind == "base":
+        fix = helpers.load_golden(f"rflow_{name}.pt")
+        out = rflow.RFLOW(**kw).sample(helpers.ToyDenoiser(dt), helpers.ToyTextEncoder(), z.clone(), prompts, "cpu",
+                                       **common)
+    else:
+        fix = helpers.load_golden(f"rflow_{kind}_{name}.pt")
+        zi, mi = helpers.rflow_inpaint_inputs(z)
+        if kind == "brushnet":
+            sched, model = rflow.RFLOW_BRUSHNET(**kw), helpers.ToyBrushDenoiser(dt)
+        else:
+            sched = rflow.RFLOW_SDEBRUSHNET(inpaint_noise_scale=helpers.SDE_NOISE_SCALE, **kw)
+            model = helpers.ToySDEDenoiser(dt)
+        out = sched.sample(model, helpers.ToyTextEncoder(), z.clone(), zi, mi, prompts, "cpu", **common)
+    assert out.dtype == torch.float32 and torch.equal(out, fix["out"])

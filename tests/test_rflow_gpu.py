@@ -68,3 +68,29 @@ def test_sample_matches_reference_golden(name):
                                        additional_args=dict(extra), mask=mask, guidance_scale=g, progress=False)
     assert ops.launches - before == kw["num_sampling_steps"]            # one fused launch per step
     assert out.dtype == torch.float32 and torch.equal(out.cpu(), fix["out"])
+
+
+@pytest.mark.parametrize("kind,name", helpers.RFLOW_BRUSH_CASES)
+def test_brushnet_samplers_match_reference_golden(kind, name):
+    """RFLOW_BRUSHNET / RFLOW_SDEBRUSHNET (rf/__init__.py:121-397) against latents of the REAL reference samplers."""
+    from magicdrive_v2_b200 import ops, rflow
+    kw, z, extra, mask, g = helpers.rflow_inputs(name, device="cuda")
+    fix = helpers.load_golden(f"rflow_{kind}_{name}.pt")
+    dt = z.dtype if z.dtype == torch.bfloat16 else torch.float32
+    zi, mi = helpers.rflow_inpaint_inputs(z)
+    if kind == "brushnet":
+        sched, model = rflow.RFLOW_BRUSHNET(**kw), helpers.ToyBrushDenoiser(dt).cuda()
+    else:
+        sched = rflow.RFLOW_SDEBRUSHNET(inpaint_noise_scale=helpers.SDE_NOISE_SCALE, **kw)
+        model = helpers.ToySDEDenoiser(dt).cuda()
+
+    class Enc(helpers.ToyTextEncoder):
+        def encode(self, prompts):
+            return {k: v.cuda() for k, v in super().encode(prompts).items()}
+
+    before = ops.launches
+    with mock.patch.object(torch, "randn_like", helpers.cpu_randn_like()):
+        out = sched.sample(model, Enc(), z.clone(), zi, mi, ["a", "b"][: z.shape[0]], "cuda",
+                           additional_args=dict(extra), mask=mask, guidance_scale=g, progress=False)
+    assert ops.launches - before == kw["num_sampling_steps"]
+    assert out.dtype == torch.float32 and torch.equal(out.cpu(), fix["out"])
