@@ -280,6 +280,9 @@ _XYZ_RANGE = (350.0, 650.0, 80.0)
 
 
 class ContinuousBBoxWithTextTempEmbedding(nn.Module, ):
+    NuScenes_bbox_classes = ["car", "truck", "construction_vehicle", "bus", "trailer", "barrier", "motorcycle",
+                             "bicycle", "pedestrian", "traffic_cone"]
+
     def __init__(self, n_classes, class_token_dim=768, trainable_class_token=False, embedder_num_freq=4,
                  proj_dims=(768, 512, 512, 768), mode="cxyz", minmax_normalize=True,
                  use_text_encoder_init=True, after_proj=False, sample_id=False, num_heads=8,
@@ -288,6 +291,7 @@ class ContinuousBBoxWithTextTempEmbedding(nn.Module, ):
         super().__init__()
         n_pts = {"cxyz": 4, "all-xyz": 8}[mode]
         self.mode, self.minmax_normalize, self.num_freqs = mode, minmax_normalize, embedder_num_freq
+        self.use_text_encoder_init = use_text_encoder_init
         pos_dim = 3 * (1 + 2 * embedder_num_freq) * n_pts
         self.bbox_proj = nn.Linear(pos_dim, proj_dims[0])
         self.second_linear = nn.Sequential(
@@ -316,6 +320,16 @@ class ContinuousBBoxWithTextTempEmbedding(nn.Module, ):
     @property
     def box_latent_shape(self):
         return self._class_tokens[0:1].shape
+
+    def prepare(self, text_encoder, classes=None):
+        """embedder.py:253-261: class tokens from the text encoder (mean over its tokens) when so configured."""
+        if self.use_text_encoder_init:
+            self.set_category_token(text_encoder, self.NuScenes_bbox_classes if classes is None else classes)
+
+    @torch.no_grad()
+    def set_category_token(self, text_encoder, class_names):
+        for idx, name in enumerate(class_names):                 # embedder.py:263-271
+            self._class_tokens[idx].copy_(text_encoder([name]).mean(dim=1)[0])
 
     def forward_feature(self, pos_emb, cls_emb):
         emb = F.silu(self.bbox_proj(pos_emb))

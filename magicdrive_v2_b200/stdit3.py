@@ -243,6 +243,19 @@ class MagicDriveSTDiT3(PreTrainedModel):
             y = y.squeeze(1)
         return y
 
+    def prepare_text_embedding(self, text_encoder):
+        """magicdrive_stdit3.py:1009-1019: class tokens of the box embedder and ``base_token`` from the text encoder
+        (``text -> caption MLP -> the prompt's tokens``); invalidates the condition cache."""
+        @torch.no_grad()
+        def text_to_embedding(text):
+            ret = text_encoder.encode(text)
+            hidden_state = self.encode_text(ret["y"], mask=None)
+            return hidden_state[:, :int(ret["mask"].sum(dim=1))]
+        self.bbox_embedder.prepare(text_to_embedding)
+        with torch.no_grad():
+            self.base_token[:] = text_to_embedding("").squeeze()
+        self.clear_condition_cache()
+
     def encode_cond_sequence(self, bbox, cams, rel_pos, y, mask, drop_cond_mask, drop_frame_mask):
         """-> [β, T', L, C] = frame(1) ‖ cam(1) ‖ text ‖ boxes (magicdrive_stdit3.py:918-961)."""
         b = len(y)
