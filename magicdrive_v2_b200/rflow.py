@@ -96,6 +96,79 @@ class RFLOW:
         return self._sample(model, text_encoder, z, prompts, device, neg_prompts, additional_args, mask,
                             guidance_scale, progress, lambda z_in, t2, z, args: model(z_in, t2, **args))
 
+    def _device_schedule(self, z, device, additional_args):
+        """-> (timesteps, add_noise timepoints [n,1,1,1,1], step sizes [steps, n]) on ``device``.  The schedule is
+        computed on the HOST (IEEE division; torch's CUDA kernels divide by a scalar through a rounded reciprocal,
+        which would move timesteps by an ulp) and uploaded once."""
+        host_args = None
+        if additional_args is not None:
+            host_args = {k: (v.cpu() if torch.is_tensor(v) else v) for k, v in additional_args.items()
+                         if k in ("height", "width", "num_frames")}
+        timesteps, dts = self.schedule(z.shape[0], "cpu", host_args)
+        keeps = [1 - t.float() / self.num_timesteps for t in timesteps]          # add_noise's timepoints
+        return ([t.to(device) for t in timesteps], [k.to(device)[:, None, None, None, None] for k in keeps],
+                dts.to(device))
+
+    @staticmethod
+    def _progress(steps, progress):
+        if progress:
+            try:
+                from tqdm import tqdm
+                return tqdm(steps, leave=False)
+            except ImportError:
+                pass
+        return steps
+
+    def _sample_slice(self, model, text_encoder, z, prompts, device, neg_prompts, additional_args, mask,
+                      guidance_scale, progress, call, per_step=None):
+        """The "slice" loop (rf/__init__.py:426-523): the conditional and the unconditional half of every step are two
+        denoiser calls at the un-doubled batch, for memory-tight runs.  The null conditions do not change between
+        steps, so they are built ONCE (the reference rebuilds them every step, ``:493-497``) and the denoiser's
+        two-entry condition cache serves both halves from the second step on.  ``call(z, t, args, st)`` with
+        ``st = per_step(z)`` drawn once per step (the SDE variant's inpaint noise is shared by the two halves)."""
+        from . import ops
+        from .inference_utils import replace_with_null_condition
+        if guidance_scale is None:
+            guidance_scale = self.cfg_scale
+        n = len(prompts)
+        model_args = text_encoder.encode(prompts)
+        if additional_args is not None:
+            model_args.update(additional_args)
+        if neg_prompts is not None:
+            y_null = text_encoder.encode(neg_prompts)["y"]
+        else:
+            y_null = text_encoder.null(n).to(device)
+        null_args = replace_with_null_condition(
+            model_args, model.camera_embedder.uncond_cam.to(device), model.frame_embedder.uncond_cam.to(device),
+            y_null, ["y", "bbox", "cams", "rel_pos", "maps"], append=False)
+        timesteps, keeps, dts = self._device_schedule(z, device, additional_args)
+        if mask is not None:
+            noise_added = mask == 1
+        z = z.contiguous()
+        for i in self._progress(range(len(timesteps)), progress):
+            t = timesteps[i]
+            x0 = keep = None
+            cond_i, null_i = model_args, null_args
+            if mask is not None:                                    # rf/__init__.py:472-481
+                x0 = z.clone()
+                x_noise = keeps[i] * x0 + (1 - keeps[i]) * torch.randn_like(x0)
+                keep = mask * self.num_timesteps >= t.unsqueeze(1)
+                z = torch.where((keep & ~noise_added)[:, None, :, None, None], x_noise, x0).contiguous()
+                x0 = x0.to(z.dtype)
+                noise_added = keep
+                cond_i, null_i = dict(model_args, x_mask=keep), dict(null_args, x_mask=keep)
+            halves = []
+            st = per_step(z) if per_step is not None else None
+            for args in (cond_i, null_i):
+                pred = call(z, t, args, st)
+                if pred.shape[1] == z.shape[1] * 2:
+                    pred = pred.chunk(2, dim=1)[0]
+                else:
+                    assert pred.shape[1] == z.shape[1]
+                halves.append(pred.float())
+            z = ops.cfg_euler_step(torch.cat(halves, 0), z, dts[i], guidance_scale, x0=x0, keep=keep)
+        return z
+
     def _sample(self, model, text_encoder, z, prompts, device, neg_prompts, additional_args, mask, guidance_scale,
                 progress, call):
         """The sampling loop shared by the three samplers; ``call(z_in, t2, z, model_args)`` is the denoiser call of
@@ -112,18 +185,7 @@ class RFLOW:
         model_args["y"] = torch.cat([model_args["y"], y_null], 0)
         if additional_args is not None:
             model_args.update(additional_args)
-
-        # The schedule is computed on the HOST (IEEE division; torch's CUDA kernels divide by a scalar through a
-        # rounded reciprocal, which would move timesteps by an ulp) and uploaded once.
-        host_args = None
-        if additional_args is not None:
-            host_args = {k: (v.cpu() if torch.is_tensor(v) else v) for k, v in additional_args.items()
-                         if k in ("height", "width", "num_frames")}
-        timesteps, dts = self.schedule(z.shape[0], "cpu", host_args)
-        keeps = [1 - t.float() / self.num_timesteps for t in timesteps]          # add_noise's timepoints
-        timesteps = [t.to(device) for t in timesteps]
-        keeps = [k.to(device)[:, None, None, None, None] for k in keeps]
-        dts = dts.to(device)
+        timesteps, keeps, dts = self._device_schedule(z, device, additional_args)
         t2 = [torch.cat([t, t], 0) for t in timesteps]
         if mask is not None:
             noise_added = mask == 1
@@ -135,14 +197,7 @@ class RFLOW:
         z_in[: z.shape[0]].copy_(z)
         z_in[z.shape[0]:].copy_(z)
 
-        steps = range(len(timesteps))
-        if progress:
-            try:
-                from tqdm import tqdm
-                steps = tqdm(steps, leave=False)
-            except ImportError:
-                pass
-        for i in steps:
+        for i in self._progress(range(len(timesteps)), progress):
             t = timesteps[i]
             x0 = keep = None
             if mask is not None:                                    # rf/__init__.py:83-93
@@ -210,3 +265,95 @@ class RFLOW_SDEBRUSHNET(RFLOW):
             return model(z_in, zi, mi, t2, t_in, self.num_timesteps, noise_inpaint_encoded=_doubled(noise), **args)
         return self._sample(model, text_encoder, z, prompts, device, neg_prompts, additional_args, mask,
                             guidance_scale, progress, call)
+
+
+@SCHEDULERS.register_module("rflow-slice")
+class RFLOW_SLICE(RFLOW):
+    """``RFLOW_SLICE`` (rf/__init__.py:426-523)."""
+
+    @torch.no_grad()
+    def sample(self, model, text_encoder, z, prompts, device, neg_prompts=None, additional_args=None, mask=None,
+               guidance_scale=None, progress=True):
+        return self._sample_slice(model, text_encoder, z, prompts, device, neg_prompts, additional_args, mask,
+                                  guidance_scale, progress, lambda z, t, args, st: model(z, t, **args))
+
+
+@SCHEDULERS.register_module("rflow-brushnet-slice")
+class RFLOW_BRUSHNET_SLICE(RFLOW_BRUSHNET):
+    """``RFLOW_BRUSHNET_SLICE`` (rf/__init__.py:525-643); the text-encoder / model device shuffling around the loop
+    (``:549,558-559,642-643``) is an offloading aid of the reference's pipeline and not reproduced."""
+
+    @torch.no_grad()
+    def sample(self, model, text_encoder, z, z_inpaint, mask_inpaint, prompts, device, neg_prompts=None,
+               additional_args=None, mask=None, guidance_scale=None, progress=True):
+        return self._sample_slice(model, text_encoder, z, prompts, device, neg_prompts, additional_args, mask,
+                                  guidance_scale, progress,
+                                  lambda z, t, args, st: model(z, z_inpaint, mask_inpaint, t, **args))
+
+
+@SCHEDULERS.register_module("rflow-sdebrushnet-slice")
+class RFLOW_SDEBRUSHNET_SLICE(RFLOW_SDEBRUSHNET):
+    """``RFLOW_SDEBRUSHNET_SLICE`` (rf/__init__.py:646-777): one ``randn_like(z)`` per step, shared by both halves."""
+
+    @torch.no_grad()
+    def sample(self, model, text_encoder, z, z_inpaint, mask_inpaint, prompts, device, neg_prompts=None,
+               additional_args=None, mask=None, guidance_scale=None, inpaint_noise_scale=None, progress=True):
+        if inpaint_noise_scale is None:
+            inpaint_noise_scale = self.inpaint_noise_scale
+        t_in = torch.tensor([inpaint_noise_scale * self.num_timesteps] * z.shape[0], device=device)
+
+        def call(z, t, args, noise):
+            return model(z, z_inpaint, mask_inpaint, t, t_in, self.num_timesteps, noise_inpaint_encoded=noise, **args)
+        return self._sample_slice(model, text_encoder, z, prompts, device, neg_prompts, additional_args, mask,
+                                  guidance_scale, progress, call, per_step=torch.randn_like)
+
+
+@SCHEDULERS.register_module("rflow-slice-repaint")
+class RFLOW_SLICE_REPAINT(RFLOW):
+    """``RFLOW_SLICE_REPAINT`` (rf/__init__.py:780-887): sampling starts from fresh noise; after every step whose
+    timestep is at or above ``ignore_mask_timestep`` the masked region is re-imposed from the reference latent noised
+    to the NEXT timestep (``z = noised(ref)·mask + z·(1 - mask)``, element-wise ``mask`` shaped like ``z``)."""
+
+    @torch.no_grad()
+    def sample(self, model, text_encoder, z, ignore_mask_timestep, prompts, device, neg_prompts=None,
+               additional_args=None, mask=None, guidance_scale=None, progress=True):
+        from . import ops
+        from .inference_utils import replace_with_null_condition
+        if guidance_scale is None:
+            guidance_scale = self.cfg_scale
+        n = len(prompts)
+        model_args = text_encoder.encode(prompts)
+        if additional_args is not None:
+            model_args.update(additional_args)
+        if neg_prompts is not None:
+            y_null = text_encoder.encode(neg_prompts)["y"]
+        else:
+            y_null = text_encoder.null(n).to(device)
+        null_args = replace_with_null_condition(
+            model_args, model.camera_embedder.uncond_cam.to(device), model.frame_embedder.uncond_cam.to(device),
+            y_null, ["y", "bbox", "cams", "rel_pos", "maps"], append=False)
+        timesteps, keeps, dts = self._device_schedule(z, device, additional_args)
+        t_first = [t[0].cpu() for t in timesteps]                   # host copies: no per-step device read-back
+        keeps.append(torch.ones(1, device=device)[:, None, None, None, None])    # "next t" after the last step is 0
+        if mask is not None:
+            assert mask.shape == z.shape
+            ref_z = z.clone()
+            z = torch.randn_like(ref_z)
+        z = z.contiguous()
+        all_frames = torch.ones([1, z.shape[2]], dtype=torch.bool, device=device)
+        cond_args, null_args = dict(model_args, x_mask=all_frames), dict(null_args, x_mask=all_frames)
+        for i in self._progress(range(len(timesteps)), progress):
+            halves = []
+            for args in (cond_args, null_args):
+                pred = model(z, timesteps[i], **args)
+                if pred.shape[1] == z.shape[1] * 2:
+                    pred = pred.chunk(2, dim=1)[0]
+                else:
+                    assert pred.shape[1] == z.shape[1]
+                halves.append(pred.float())
+            z = ops.cfg_euler_step(torch.cat(halves, 0), z, dts[i], guidance_scale)
+            if mask is not None and bool(t_first[i] >= ignore_mask_timestep * self.num_timesteps):
+                x0 = ref_z.clone()
+                x_noise = keeps[i + 1] * x0 + (1 - keeps[i + 1]) * torch.randn_like(x0)
+                z = (x_noise * mask + z * (1 - mask)).contiguous()
+        return z

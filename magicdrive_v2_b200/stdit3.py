@@ -326,16 +326,20 @@ class MagicDriveSTDiT3(PreTrainedModel):
 
     @torch.no_grad()
     def _conditions(self, ops, dtype, y, mask, bbox, cams, rel_pos, maps, drop_cond_mask,
-                    drop_frame_mask, geom):
+                    drop_frame_mask, geom, drop_key=None):
         """Returns the cached timestep-independent operands:
         cond [β,Tc,L,C], per-block cross-attn K/V, map tokens ``m`` [b·T·S, C] (before_proj applied)."""
         (b, NC, T, Hp, Wp, h_pad, x_thw) = geom
-        flat = [y, mask, cams, rel_pos, maps, drop_cond_mask, drop_frame_mask, geom, dtype]
+        # (drop masks the caller left at None are materialised anew by every forward: key them as None, not by identity)
+        dk = drop_key if drop_key is not None else (drop_cond_mask, drop_frame_mask)
+        flat = [y, mask, cams, rel_pos, maps, dk[0], dk[1], geom, dtype]
         if bbox is not None:
             flat += [bbox[k] for k in sorted(bbox)]
         key = self._condition_key(flat)
-        if self.cache_conditions and self._cond_cache is not None and self._cond_cache[0] == key:
-            return self._cond_cache[1]
+        # two entries: the "slice" samplers alternate between the conditional and the null condition set
+        for entry in (self._cond_cache or ()) if self.cache_conditions else ():
+            if entry[0] == key:
+                return entry[1]
         C = self.hidden_size
 
         def cast(t):     # callers hand conditions in the model dtype (inference_magicdrive.py:345-358); be lenient
@@ -376,7 +380,7 @@ class MagicDriveSTDiT3(PreTrainedModel):
         out = dict(cond=cond, y_kv=y_kv, m=m.view(b, T, S, C), L=L, y_frames=Tc)
         if self.cache_conditions:
             # the key holds ids / data pointers: keep the keyed tensors alive so neither can be recycled
-            self._cond_cache = (key, out, flat)
+            self._cond_cache = [(key, out, flat)] + list(self._cond_cache or ())[:1]
         return out
 
     # ------------------------------------------------------------------------------------------
@@ -400,6 +404,7 @@ class MagicDriveSTDiT3(PreTrainedModel):
         dtype = self.x_embedder.proj.weight.dtype
         dev = x.device
         b, real_T = x.size(0), rel_pos.size(1)
+        drop_key = (drop_cond_mask, drop_frame_mask)
         if drop_cond_mask is None:
             drop_cond_mask = torch.ones((b,), device=dev, dtype=x.dtype)
         if drop_frame_mask is None:
@@ -451,7 +456,7 @@ class MagicDriveSTDiT3(PreTrainedModel):
         # --- conditions (cached) ---
         geom = (b, NC, T, Hp, Wp, h_pad, (Tx, Hx, Wx))
         cnd = self._conditions(ops, dtype, y, mask, bbox, cams, rel_pos, maps, drop_cond_mask,
-                               drop_frame_mask, geom)
+                               drop_frame_mask, geom, drop_key=drop_key)
 
         # --- embed x: two streams share one patch gather ---
         d = Dims(b=b, NC=NC, T=T, S=Sl, C=C, H=NH, D=C // NH)

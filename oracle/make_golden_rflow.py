@@ -41,6 +41,12 @@ def main():
         torch.save(dict(case=name, kind=kind, out=out.clone()),
                    os.path.join(ROOT, "tests", "golden", f"rflow_{kind}_{name}.pt"))
         print(kind, name, tuple(out.shape), out.dtype, out.float().abs().mean().item())
+    for kind, name in helpers.RFLOW_SLICE_CASES:        # the "slice" family, rf/__init__.py:426-887
+        with mock.patch.object(torch, "randn_like", helpers.cpu_randn_like()):
+            out = helpers.run_slice_sampler(rf, kind, name)
+        torch.save(dict(case=name, kind=kind, out=out.clone()),
+                   os.path.join(ROOT, "tests", "golden", f"rflow_{kind}_{name}.pt"))
+        print(kind, name, tuple(out.shape), out.dtype, out.float().abs().mean().item())
 
 
 if __name__ == "__main__":

@@ -68,11 +68,21 @@ def load_reference_sampler():
         return sys.modules[name]
     pkg = os.path.join(REF_ROOT, "magicdrivedit")
     _ns("magicdrivedit.schedulers", os.path.join(pkg, "schedulers"))      # skip iddpm / dpm-solver imports
-    iu = types.ModuleType("magicdrivedit.utils.inference_utils")          # pulls mmcv / datasets; sample() never calls it
-
-    def replace_with_null_condition(*a, **k):
-        raise NotImplementedError("oracle stub")
-
-    iu.replace_with_null_condition = replace_with_null_condition
-    sys.modules.setdefault("magicdrivedit.utils.inference_utils", iu)
+    # magicdrivedit/utils/inference_utils.py imports mmcv / datasets at module level; the samplers only need its two
+    # null-condition builders, so exactly those two function definitions of the REAL file are compiled (from where the
+    # file lies) into a stand-in module
+    import ast
+    path = os.path.join(pkg, "utils", "inference_utils.py")
+    with open(path) as f:
+        tree = ast.parse(f.read(), filename=path)
+    wanted = ("replace_with_null_condition", "add_null_condition")
+    tree.body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in wanted]
+    assert len(tree.body) == len(wanted)
+    iu = types.ModuleType("magicdrivedit.utils.inference_utils")
+    import copy
+    import torch
+    from einops import repeat
+    iu.__dict__.update(torch=torch, repeat=repeat, deepcopy=copy.deepcopy)
+    exec(compile(tree, path, "exec"), iu.__dict__)
+    sys.modules["magicdrivedit.utils.inference_utils"] = iu
     return importlib.import_module(name)

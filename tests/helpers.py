@@ -50,11 +50,30 @@ class ToyDenoiser(torch.nn.Module):
 
     def __init__(self, dtype=torch.bfloat16):
         super().__init__()
+        import types
         self.w = torch.nn.Parameter(torch.tensor(0.3, dtype=dtype))
+        # what the "slice" samplers read off the denoiser (rf/__init__.py:494-496); eighths, so sums stay exact
+        self.camera_embedder = types.SimpleNamespace(uncond_cam=torch.arange(21).view(3, 7).float() / 8 - 1)
+        self.frame_embedder = types.SimpleNamespace(uncond_cam=torch.arange(12).view(3, 4).float() / 8 - 0.5)
+
+    @property
+    def device(self):
+        return self.w.device
+
+    @staticmethod
+    def condition_term(cams, rel_pos, bbox, maps):
+        """Per-sample scalar that depends on every condition the null builders touch; all inputs are small multiples
+        of 1/8, so the sums are exact in fp32 in any order (CPU and GPU agree to the bit)."""
+        def tot(t):
+            return t.float().flatten(1).sum(dim=1)
+        c = tot(cams) + tot(rel_pos[..., :3, :]) + tot(bbox["bboxes"]) + tot(bbox["masks"]) + tot(maps)
+        return (c * (1.0 / 64)).view(-1, 1, 1, 1, 1)
 
     def forward(self, x, timestep, y, x_mask=None, **kwargs):
         xf = x.to(self.w.dtype).float()
         s = y.float().view(-1, 1, 1, 1, 1)
+        if "cams" in kwargs:
+            s = s + self.condition_term(kwargs["cams"], kwargs["rel_pos"], kwargs["bbox"], kwargs["maps"])
         tt = (timestep.float() * 0.001).view(-1, 1, 1, 1, 1)      # (no division: CUDA divides through a reciprocal)
         out = xf * 0.3
         out = out + s * tt
@@ -68,7 +87,7 @@ class ToyBrushDenoiser(ToyDenoiser):
     """Same exact-arithmetic stand-in with the BrushNet call signature (magicdrive_stdit3.py:1466-1487)."""
 
     def forward(self, x, x_inpaint, mask_inpaint, timestep, y, x_mask=None, **kwargs):
-        out = ToyDenoiser.forward(self, x, timestep, y, x_mask=x_mask)
+        out = ToyDenoiser.forward(self, x, timestep, y, x_mask=x_mask, **kwargs)
         return out + x_inpaint.float() * mask_inpaint.float() * 0.5
 
 
@@ -77,7 +96,7 @@ class ToySDEDenoiser(ToyDenoiser):
 
     def forward(self, x, x_inpaint, mask_inpaint, timestep, timestep_inpaint, num_timesteps, y,
                 noise_inpaint_encoded=None, x_mask=None, **kwargs):
-        out = ToyDenoiser.forward(self, x, timestep, y, x_mask=x_mask)
+        out = ToyDenoiser.forward(self, x, timestep, y, x_mask=x_mask, **kwargs)
         out = out + x_inpaint.float() * mask_inpaint.float() * 0.5
         lvl = (timestep_inpaint.float() * (1.0 / 1024)).view(-1, 1, 1, 1, 1) * (num_timesteps * (1.0 / 1024))
         return out + noise_inpaint_encoded.float() * lvl
@@ -89,6 +108,59 @@ def rflow_inpaint_inputs(z):
     zi = torch.randn(z.shape, generator=gen).to(z.device)
     mi = (torch.rand((z.shape[0], 1) + tuple(z.shape[2:]), generator=gen) > 0.4).float().to(z.device)
     return zi, mi
+
+
+def rflow_slice_conditions(z):
+    """cams / rel_pos / bbox / maps for the "slice" samplers' toy runs (values are eighths, see condition_term)."""
+    gen = torch.Generator().manual_seed(17)
+    n, T = z.shape[0], z.shape[2]
+
+    def eighths(*shape):
+        return (torch.randint(-4, 5, shape, generator=gen).float() / 8).to(z.device)
+    return dict(cams=eighths(n, T, 1, 3, 7), rel_pos=eighths(n, T, 1, 4, 4), maps=eighths(n, T, 2, 4, 4),
+                bbox=dict(bboxes=eighths(n, T, 2, 8, 3), classes=torch.ones(n, T, 2, dtype=torch.long, device=z.device),
+                          masks=torch.ones(n, T, 2, device=z.device)))
+
+
+# (sampler kind, RFLOW_CASES entry): the un-doubled "slice" family, rf/__init__.py:426-887
+RFLOW_SLICE_CASES = [("slice", "plain"), ("slice", "masked"), ("brushnet-slice", "masked"),
+                     ("sdebrushnet-slice", "cog_bf16"), ("sdebrushnet-slice", "masked"), ("slice-repaint", "plain"),
+                     ("slice-repaint", "cog_bf16")]
+REPAINT_IGNORE_T = 0.3
+
+
+def run_slice_sampler(mod, kind, name, device="cpu"):
+    """Runs sampler ``kind`` of module ``mod`` (the reference's ``schedulers.rf`` or ours) on the toy fixtures."""
+    kw, z, extra, mask, g = rflow_inputs(name, device=device)
+    dt = z.dtype if z.dtype == torch.bfloat16 else torch.float32
+    extra = dict(extra, **rflow_slice_conditions(z))
+    zi, mi = rflow_inpaint_inputs(z)
+    prompts = ["a", "b"][: z.shape[0]]
+
+    class Enc(ToyTextEncoder):
+        class t5:                                         # the brushnet slice samplers park the T5 model (:549,558)
+            class model:
+                device = "cpu"
+                to = staticmethod(lambda d: None)
+
+        def encode(self, p):
+            return {k: v.to(device) for k, v in super().encode(p).items()}
+    common = dict(additional_args=extra, guidance_scale=g, progress=False)
+    if kind == "slice":
+        return mod.RFLOW_SLICE(**kw).sample(ToyDenoiser(dt).to(device), Enc(), z.clone(), prompts, device, mask=mask,
+                                            **common)
+    if kind == "brushnet-slice":
+        return mod.RFLOW_BRUSHNET_SLICE(**kw).sample(ToyBrushDenoiser(dt).to(device), Enc(), z.clone(), zi, mi,
+                                                     prompts, device, mask=mask, **common)
+    if kind == "sdebrushnet-slice":
+        sched = mod.RFLOW_SDEBRUSHNET_SLICE(inpaint_noise_scale=SDE_NOISE_SCALE, **kw)
+        return sched.sample(ToySDEDenoiser(dt).to(device), Enc(), z.clone(), zi, mi, prompts, device, mask=mask,
+                            **common)
+    assert kind == "slice-repaint"
+    gen = torch.Generator().manual_seed(19)
+    emask = (torch.rand(z.shape, generator=gen) > 0.5).float().to(device)          # element-wise, shaped like z
+    return mod.RFLOW_SLICE_REPAINT(**kw).sample(ToyDenoiser(dt).to(device), Enc(), z.clone(), REPAINT_IGNORE_T, prompts,
+                                                device, mask=emask, **common)
 
 
 RFLOW_BRUSH_CASES = [("brushnet", "plain"), ("brushnet", "masked"), ("sde", "cog_bf16"), ("sde", "masked")]

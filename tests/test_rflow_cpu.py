@@ -123,3 +123,51 @@ def test_sampler_host_logic_matches_reference_golden(kind, name, monkeypatch):
             model = helpers.ToySDEDenoiser(dt)
         out = sched.sample(model, helpers.ToyTextEncoder(), z.clone(), zi, mi, prompts, "cpu", **common)
     assert out.dtype == torch.float32 and torch.equal(out, fix["out"])
+
+
+@pytest.mark.parametrize("kind,name", helpers.RFLOW_SLICE_CASES)
+def test_slice_samplers_host_logic_matches_reference_golden(kind, name, monkeypatch):
+    """The un-doubled "slice" family (rf/__init__.py:426-887: two denoiser calls per step, null conditions from
+    ``replace_with_null_condition``, repaint re-noising) with the fused step replaced by its eager specification:
+    bit-exact vs latents of the REAL reference samplers."""
+    from magicdrive_v2_b200 import ops
+    monkeypatch.setattr(ops, "cfg_euler_step", _spec_cfg_euler_step)
+    monkeypatch.setattr(torch, "randn_like", helpers.cpu_randn_like())
+    fix = helpers.load_golden(f"rflow_{kind}_{name}.pt")
+    out = helpers.run_slice_sampler(rflow, kind, name)
+    assert out.dtype == fix["out"].dtype and torch.equal(out, fix["out"])
+
+
+def test_null_condition_builders():
+    """inference_utils.py:144-296 mirrors: structure, the rel_pos row-drop quirk, append / prepend order, errors."""
+    from magicdrive_v2_b200.inference_utils import add_null_condition, replace_with_null_condition
+    z = torch.zeros(2, 6, 3, 4, 4)
+    args = dict(y=torch.ones(2, 1, 5, 8), mask=torch.ones(1, 5), height=torch.tensor([224.0]), fps=12,
+                mv_order_map={0: [1]}, **helpers.rflow_slice_conditions(z))
+    uc, ur = torch.arange(21.0).view(3, 7), torch.arange(12.0).view(3, 4)
+    y_null = torch.zeros(2, 1, 5, 8)
+    keys = ["y", "bbox", "cams", "rel_pos", "maps"]
+    out = replace_with_null_condition(args, uc, ur, y_null, keys, append=False)
+    assert keys == [] and out["y"] is y_null and out["height"] is args["height"] and out["fps"] == 12
+    assert out["cams"].shape == args["cams"].shape and torch.equal(out["cams"][1, 2, 0], uc)
+    assert out["rel_pos"].shape == (2, 3, 1, 3, 4) and torch.equal(out["rel_pos"][0, 0, 0], ur)
+    assert all(torch.count_nonzero(v) == 0 for v in out["bbox"].values()) and torch.count_nonzero(out["maps"]) == 0
+    assert torch.equal(out["mask"], args["mask"]) and out["mask"] is not args["mask"]
+    both = replace_with_null_condition(args, uc, ur, y_null, ["y", "cams", "maps"], append=True)
+    assert both["y"].shape[0] == 4 and torch.equal(both["cams"][:2], args["cams"]) and torch.equal(both["cams"][3, 0, 0], uc)
+    assert both["bbox"]["bboxes"].shape[0] == 4 and both["mask"].shape[0] == 2 and both["rel_pos"].shape[0] == 4
+    with pytest.raises(RuntimeError):
+        replace_with_null_condition(dict(y=args["y"]), uc, ur, y_null, ["y", "cams"])
+    dbl = add_null_condition(args, uc, ur, prepend=True, use_map0=True)
+    assert torch.equal(dbl["cams"][2:], args["cams"]) and torch.equal(dbl["cams"][0, 0, 0], uc)
+    assert dbl["rel_pos"].shape == (4, 3, 1, 3, 4) and torch.count_nonzero(dbl["maps"][:2]) == 0
+    assert dbl["y"].shape[0] == 4 and dbl["fps"] == 12
+    dbl = add_null_condition(args, uc, ur)
+    assert torch.equal(dbl["maps"][:2], dbl["maps"][2:]) and torch.equal(dbl["cams"][:2], args["cams"])
+
+
+def test_slice_samplers_registered():
+    for name, cls in [("rflow-slice", rflow.RFLOW_SLICE), ("rflow-brushnet-slice", rflow.RFLOW_BRUSHNET_SLICE),
+                      ("rflow-sdebrushnet-slice", rflow.RFLOW_SDEBRUSHNET_SLICE),
+                      ("rflow-slice-repaint", rflow.RFLOW_SLICE_REPAINT)]:
+        assert isinstance(SCHEDULERS.build(dict(type=name, num_sampling_steps=2)), cls)

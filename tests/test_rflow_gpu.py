@@ -94,3 +94,15 @@ def test_brushnet_samplers_match_reference_golden(kind, name):
                            additional_args=dict(extra), mask=mask, guidance_scale=g, progress=False)
     assert ops.launches - before == kw["num_sampling_steps"]
     assert out.dtype == torch.float32 and torch.equal(out.cpu(), fix["out"])
+
+
+@pytest.mark.parametrize("kind,name", helpers.RFLOW_SLICE_CASES)
+def test_slice_samplers_match_reference_golden(kind, name):
+    """The un-doubled "slice" family (rf/__init__.py:426-887) against latents of the REAL reference samplers."""
+    from magicdrive_v2_b200 import ops, rflow
+    fix = helpers.load_golden(f"rflow_{kind}_{name}.pt")
+    before = ops.launches
+    with mock.patch.object(torch, "randn_like", helpers.cpu_randn_like()):
+        out = helpers.run_slice_sampler(rflow, kind, name, device="cuda")
+    assert ops.launches - before == helpers.RFLOW_CASES[name][0]["num_sampling_steps"]
+    assert out.dtype == torch.float32 and torch.equal(out.cpu(), fix["out"])
