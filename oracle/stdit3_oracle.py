@@ -431,7 +431,10 @@ def forward(sd, cfg, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, wid
     scale = (height[0].item() * width[0].item()) ** 0.5 / cfg.get("input_sq_size", 512)
     pos = pos_embed(C, H, W, scale, base_size, dtype)
 
-    fps_e = t_embed(p.sub("fps_embedder"), fps.unsqueeze(1).reshape(-1), dtype).reshape(B, -1)
+    fps_ = fps.unsqueeze(1)
+    if fps_.shape[0] != B:                                   # SizeEmbedder.forward, blocks.py:999-1003
+        fps_ = fps_.repeat(B // fps_.shape[0], 1)
+    fps_e = t_embed(p.sub("fps_embedder"), fps_.reshape(-1), dtype).reshape(B, -1)
     t = t_embed(p.sub("t_embedder"), timestep, dtype) + fps_e
     t_mlp = linear(p, "t_block.1", F.silu(t))
     t0 = t0_mlp = None
