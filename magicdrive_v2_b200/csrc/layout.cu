@@ -476,6 +476,161 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_kernel(const
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// bf16 production path for LONG clips (8 < T <= 32, e.g. 65 pixel frames -> T = 17): same four phases, but a CTA
+// owns ONE token column and a GROUP of HG heads, so the staged q|k|v slices of all T frames stay near 60 KB and
+// three CTAs fit an SM (a whole column at T = 17 is 118 KB: one CTA per SM, nothing in flight while it computes).
+// Shared-memory row t = [q slice | k slice | v slice] of HG·D bf16 each (three bulk copies per frame, 1152 B at
+// HG = 8, D = 72), pitch skewed by 80 B like above.
+//   A  RoPE on q and k in place (+ scale on q)
+//   B  item = (head, t_q, t_k): one score -> bf16, into a [HG][T][ceil4(T)] fp32 table behind the rows; then
+//      item = (head, t_q): fp32 softmax over its table row, probabilities rounded to bf16 in place.  (One thread per
+//      (head, t_q) doing all T dot products kept 136 of 256 threads busy on a ~3000-instruction serial chain:
+//      3.6 ms per launch at T = 17.)
+//   C  item = (t_q, head, 8-dim slice): out = sum_k P[t_q][k] v[k], written over the k slice of row t_q
+//   D  one bulk store per frame
+// The first version sent these shapes to the warp-per-(column, head) kernel above: 23.7 ms per launch at T = 17
+// (127 GB/s), 38 % of the 65-frame step.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_long_kernel(const bf16* __restrict__ qkv, int64_t ld,
+                                                                               const float* __restrict__ cos_t,
+                                                                               const float* __restrict__ sin_t,
+                                                                               bf16* __restrict__ out, int64_t ldo,
+                                                                               int64_t n_cols, int Tn, int S, int H,
+                                                                               int D, int HG, float scale) {
+  using namespace sm100;
+  extern __shared__ __align__(128) uint8_t ta_smem[];
+  const int C = H * D, W = HG * D;                      // elements per q (k, v) slice of the head group
+  const int part_bytes = W * 2, pitch = 3 * part_bytes + TA_PAD;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(ta_smem + Tn * pitch);
+  const int tid = threadIdx.x;
+  const int n_groups = H / HG;
+  const int64_t col = (int64_t)blockIdx.x / n_groups;
+  const int hg = (int)((int64_t)blockIdx.x - col * n_groups);
+  const int64_t beta = col / S, s = col - beta * S;
+  const int64_t row0 = beta * Tn * S + s;               // global row of frame 0; frame t is row0 + t·S
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+    mbar_expect_tx(bar, (uint32_t)(Tn * 3 * part_bytes));
+    for (int t = 0; t < Tn; ++t) {
+      const bf16* src = qkv + (row0 + (int64_t)t * S) * ld + (int64_t)hg * W;
+#pragma unroll
+      for (int part = 0; part < 3; ++part)
+        bulk_g2s(ta_smem + t * pitch + part * part_bytes, src + (int64_t)part * C, (uint32_t)part_bytes, bar);
+    }
+  }
+  __syncthreads();                                      // barrier init visible to the waiters
+  mbar_wait(bar, 0);
+
+  const int vpp = W / 8;                                // 16-byte vectors per slice
+  const int vph = D / 8;                                // ... per head
+  // ---- A: RoPE on q and k ----
+  for (int i = tid; i < Tn * 2 * vpp; i += TA_THREADS) {
+    const int v = i % vpp, part = (i / vpp) & 1, t = i / (2 * vpp);
+    const int d0 = (v % vph) * 8;
+    uint4* ptr = reinterpret_cast<uint4*>(ta_smem + t * pitch + part * part_bytes + v * 16);
+    Vec16<bf16> x;
+    x.raw = *ptr;
+    float f[8], o[8];
+    x.unpack(f);
+    const float4 c0 = *reinterpret_cast<const float4*>(cos_t + t * D + d0);
+    const float4 c1 = *reinterpret_cast<const float4*>(cos_t + t * D + d0 + 4);
+    const float4 s0 = *reinterpret_cast<const float4*>(sin_t + t * D + d0);
+    const float4 s1 = *reinterpret_cast<const float4*>(sin_t + t * D + d0 + 4);
+    const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+    const float sn[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+    for (int e = 0; e < 8; e += 2) {
+      o[e] = f[e] * cs[e] - f[e + 1] * sn[e];
+      o[e + 1] = f[e + 1] * cs[e + 1] + f[e] * sn[e + 1];
+    }
+    x.pack(o);
+    if (part == 0) {                                    // q = (rope(q) in bf16) * scale, in bf16
+      x.unpack(f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] *= scale;
+      x.pack(f);
+    }
+    *ptr = x.raw;
+  }
+  __syncthreads();
+  // ---- B1: item = (head, t_q, t_k): one score, rounded to bf16 like the reference's q @ k^T ----
+  const int Tp = (Tn + 3) & ~3;
+  float* sc = reinterpret_cast<float*>(ta_smem + Tn * pitch + 16);      // [HG][Tn][Tp] scores, then probabilities
+  for (int i = tid; i < HG * Tn * Tn; i += TA_THREADS) {
+    const int tk = i % Tn, tq = (i / Tn) % Tn, h = i / (Tn * Tn);
+    const uint8_t* qs = ta_smem + tq * pitch + h * D * 2;
+    const uint8_t* ks = ta_smem + tk * pitch + part_bytes + h * D * 2;
+    float acc = 0.f;
+    for (int j = 0; j < vph; ++j) {
+      Vec16<bf16> qv, kv;
+      qv.raw = *reinterpret_cast<const uint4*>(qs + j * 16);
+      kv.raw = *reinterpret_cast<const uint4*>(ks + j * 16);
+      float q[8], k[8];
+      qv.unpack(q);
+      kv.unpack(k);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc += q[e] * k[e];
+    }
+    sc[(h * Tn + tq) * Tp + tk] = __bfloat162float(__float2bfloat16_rn(acc));
+  }
+  __syncthreads();
+  // ---- B2: item = (head, t_q): fp32 softmax over its row, probabilities rounded to bf16, zero padding ----
+  for (int i = tid; i < HG * Tn; i += TA_THREADS) {
+    float* row = sc + i * Tp;                           // i = head·Tn + t_q
+    float mx = -INFINITY;
+    for (int t = 0; t < Tn; ++t) mx = fmaxf(mx, row[t]);
+    float den = 0.f;
+    for (int t = 0; t < Tn; ++t) {
+      const float e = __expf(row[t] - mx);
+      row[t] = e;
+      den += e;
+    }
+    const float inv = 1.f / den;
+    for (int t = 0; t < Tn; ++t) row[t] = __bfloat162float(__float2bfloat16_rn(row[t] * inv));
+    for (int t = Tn; t < Tp; ++t) row[t] = 0.f;
+  }
+  __syncthreads();
+  // ---- C: out[t_q][8 dims] = sum_k P[t_q][k] v[k][8 dims], written over the k slice of row t_q ----
+  for (int i = tid; i < Tn * HG * vph; i += TA_THREADS) {
+    const int j = i % vph, h = (i / vph) % HG, tq = i / (vph * HG);
+    const float4* pp = reinterpret_cast<const float4*>(sc + (h * Tn + tq) * Tp);
+    const uint8_t* vbase = ta_smem + 2 * part_bytes + h * D * 2 + j * 16;
+    float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int t4 = 0; t4 * 4 < Tn; ++t4) {
+      const float4 p4 = pp[t4];
+      const float pr[4] = {p4.x, p4.y, p4.z, p4.w};
+#pragma unroll
+      for (int e4 = 0; e4 < 4; ++e4) {
+        const int t = t4 * 4 + e4;
+        if (t < Tn) {
+          Vec16<bf16> vv;
+          vv.raw = *reinterpret_cast<const uint4*>(vbase + t * pitch);
+          float v[8];
+          vv.unpack(v);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) o[e] += pr[e4] * v[e];
+        }
+      }
+    }
+    Vec16<bf16> ov;
+    ov.pack(o);
+    *reinterpret_cast<uint4*>(ta_smem + tq * pitch + part_bytes + h * D * 2 + j * 16) = ov.raw;
+  }
+  fence_async_smem();                                   // generic-proxy writes -> visible to the bulk stores
+  __syncthreads();
+  // ---- D: one output slice per frame ----
+  if (tid == 0) {
+    for (int t = 0; t < Tn; ++t)
+      bulk_s2g(out + (row0 + (int64_t)t * S) * ldo + (int64_t)hg * W, ta_smem + t * pitch + part_bytes,
+               (uint32_t)part_bytes);
+    bulk_commit();
+    bulk_wait_read0();                                  // shared memory must outlive the reads
+  }
+}
+
+
 template <typename T>
 static int launch_temporal(const void* qkv, int64_t ld, const float* c, const float* s, void* out, int64_t ldo,
                            int B, int Tn, int S, int H, int D, float scale, cudaStream_t st) {
@@ -505,6 +660,31 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
 #undef TS_CASE
       MDV2_CHECK_LAUNCH("temporal_attention");
       return MDV2_OK;
+    }
+    if (!legacy && Tn > 8 && Tn <= 32 && D % 8 == 0 && ld % 8 == 0 && ldo % 8 == 0 && ((uintptr_t)qkv % 16 == 0) &&
+        ((uintptr_t)out % 16 == 0) && ((uintptr_t)c % 16 == 0) && ((uintptr_t)s % 16 == 0)) {
+      // largest head group (a divisor of H, at most 8 heads) whose staged frames + score table leave room for three
+      // CTAs per SM
+      const int Tp = (Tn + 3) & ~3;
+      auto smem_long = [&](int g) { return (size_t)Tn * (3 * g * D * 2 + TA_PAD) + 16 + (size_t)g * Tn * Tp * 4; };
+      int HG = 0;
+      for (int g = H < 8 ? H : 8; g >= 1; --g)
+        if (H % g == 0 && smem_long(g) <= 75 * 1024) {
+          HG = g;
+          break;
+        }
+      const int64_t n_ctas = (int64_t)B * S * (HG ? H / HG : 0);
+      if (HG && n_ctas <= 0x7fffffff) {
+        static bool configured = false;
+        if (!configured) {
+          cudaFuncSetAttribute(temporal_attn_smem_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024);
+          configured = true;
+        }
+        temporal_attn_smem_long_kernel<<<(unsigned)n_ctas, TA_THREADS, smem_long(HG), st>>>(
+            (const bf16*)qkv, ld, c, s, (bf16*)out, ldo, (int64_t)B * S, Tn, S, H, D, HG, scale);
+        MDV2_CHECK_LAUNCH("temporal_attention");
+        return MDV2_OK;
+      }
     }
     if (Tn <= 8 && D % 8 == 0 && D <= 128 && ld % 8 == 0 && ldo % 8 == 0 && ((uintptr_t)qkv % 16 == 0) &&
         ((uintptr_t)out % 16 == 0)) {

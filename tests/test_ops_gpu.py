@@ -154,6 +154,26 @@ def test_temporal_attention(dtype, T, D):
     assert rel_l2(out, ref) < 2 * TOL[dtype]
 
 
+@pytest.mark.parametrize("T,H,D", [(9, 16, 72), (13, 6, 64), (17, 16, 72), (17, 3, 72), (24, 8, 64), (32, 16, 64),
+                                   (32, 4, 40)])
+def test_temporal_attention_long_clips(T, H, D):
+    """8 < T <= 32 in bf16: the head-group staged kernel (one column x <= 8 heads per CTA; 65 pixel frames -> T = 17);
+    the last case has a head too narrow for the old in-slice probability table."""
+    dtype, B, S = torch.bfloat16, 2, 37
+    qkv = rnd(B * T * S, 3 * H * D, dtype=dtype, seed=T)
+    ang = torch.arange(T, dtype=torch.float32)[:, None] * (1.0 / 10000 ** (torch.arange(0, D, 2).float() / D))[None]
+    ang = ang.repeat_interleave(2, dim=-1).to(DEV)
+    cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
+    out, ref = (torch.full((B * T * S, H * D), float("nan"), dtype=dtype, device=DEV) for _ in range(2))
+    ops().temporal_attention(qkv, cos, sin, out, B, T, S, H, D, D ** -0.5)
+    spec_ops.temporal_attention(qkv, cos, sin, ref, B, T, S, H, D, D ** -0.5)
+    assert torch.isfinite(out).all()
+    assert rel_l2(out, ref) < 2 * TOL[dtype]
+    # every frame / head / dim slice individually (a mis-indexed slice hides in a global norm)
+    err = (out.float() - ref.float()).view(B, T, S, H, D).abs().amax(dim=(0, 2, 4))
+    assert (err < 0.05 * ref.float().abs().max()).all(), err
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_patchify_unpatchify_bit_exact(dtype):
     b, NC, Cin, T, Hx, Wx, Hp, Wp = 2, 3, 4, 2, 7, 10, 5, 5
