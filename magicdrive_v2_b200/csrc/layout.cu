@@ -313,6 +313,162 @@ __global__ void __launch_bounds__(256) temporal_attn_vec_kernel(const bf16* __re
   }
 }
 
+// warp-level bf16 tensor-core tiles for the long-clip temporal attention: 17 x 17 x 72 per (column, head) is far below a
+// tcgen05 tile (M = 128), so this is the one place the library uses mma.sync — operands stay bf16 in shared memory and
+// the bf16 -> fp32 unpacking that made up ~45 % of the scalar version's instructions disappears.
+__device__ __forceinline__ void mma_bf16_k16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void mma_bf16_k8(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a0), "r"(a1), "r"(b0));
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&v);
+}
+__device__ __forceinline__ float round_bf16(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+
+// One head of one token column, one warp: scores = q k^T (bf16-rounded), fp32 softmax over the Tn keys, probabilities
+// rounded to bf16, out = P v written over the head's k slice.  Tn <= 32.  Fragment layouts of m16n8k16 / m16n8k8
+// (g = lane / 4, i = lane % 4): A rows g, g+8, column pairs 2i (+8); B column g, row pairs 2i (+8); C rows g, g+8,
+// columns 2i, 2i+1.  The C fragments of two adjacent key tiles are exactly the A fragment of P for the second product.
+__device__ __forceinline__ void temporal_head_mma(uint8_t* rows, int pitch, int part_bytes, int Tn, int D) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, i2 = (lane & 3) * 2;
+  const int last = Tn - 1;
+  const int n_mt = (Tn + 15) >> 4;                      // query tiles of 16 (1 or 2)
+  float c[2][4][4];
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) c[mt][nt][e] = 0.f;
+  // rows beyond the clip are clamped to the last frame: their scores are masked / their outputs never stored
+  const uint8_t* qrow[2][2];
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt) {
+    qrow[mt][0] = rows + min(mt * 16 + g, last) * pitch;
+    qrow[mt][1] = rows + min(mt * 16 + g + 8, last) * pitch;
+  }
+  const uint8_t* krow[4];
+#pragma unroll
+  for (int nt = 0; nt < 4; ++nt) krow[nt] = rows + min(nt * 8 + g, last) * pitch + part_bytes;
+  const int n_nt = (Tn + 7) >> 3;                       // key tiles of 8 that hold at least one frame
+  int k0 = 0;
+  for (; k0 + 16 <= D; k0 += 16) {
+    const int off = (k0 + i2) * 2;
+    uint32_t a[2][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+      a[mt][0] = *reinterpret_cast<const uint32_t*>(qrow[mt][0] + off);
+      a[mt][1] = *reinterpret_cast<const uint32_t*>(qrow[mt][1] + off);
+      a[mt][2] = *reinterpret_cast<const uint32_t*>(qrow[mt][0] + off + 16);
+      a[mt][3] = *reinterpret_cast<const uint32_t*>(qrow[mt][1] + off + 16);
+    }
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      if (nt < n_nt) {
+        const uint32_t b0 = *reinterpret_cast<const uint32_t*>(krow[nt] + off);
+        const uint32_t b1 = *reinterpret_cast<const uint32_t*>(krow[nt] + off + 16);
+        mma_bf16_k16(c[0][nt], a[0], b0, b1);
+        if (n_mt > 1) mma_bf16_k16(c[1][nt], a[1], b0, b1);
+      }
+    }
+  }
+  if (k0 < D) {                                         // D = 16 m + 8: one k8 step for the tail
+    const int off = (k0 + i2) * 2;
+    uint32_t a[2][2];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+      a[mt][0] = *reinterpret_cast<const uint32_t*>(qrow[mt][0] + off);
+      a[mt][1] = *reinterpret_cast<const uint32_t*>(qrow[mt][1] + off);
+    }
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      if (nt < n_nt) {
+        const uint32_t b0 = *reinterpret_cast<const uint32_t*>(krow[nt] + off);
+        mma_bf16_k8(c[0][nt], a[0][0], a[0][1], b0);
+        if (n_mt > 1) mma_bf16_k8(c[1][nt], a[1][0], a[1][1], b0);
+      }
+    }
+  }
+  // softmax per query row: a row lives in the four lanes of a quad (elements 0,1 -> row g; 2,3 -> row g + 8)
+  uint32_t pa[2][2][4];                                 // P as A fragments: [query tile][key block of 16][4]
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt) {
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      float mx = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int tk = nt * 8 + i2 + e;
+          float& v = c[mt][nt][half * 2 + e];
+          v = tk < Tn ? round_bf16(v) : -INFINITY;      // q @ k^T leaves the GEMM in bf16
+          mx = fmaxf(mx, v);
+        }
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      float den = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          float& v = c[mt][nt][half * 2 + e];
+          v = __expf(v - mx);                           // masked keys: exp(-inf) = 0
+          den += v;
+        }
+      den += __shfl_xor_sync(0xffffffffu, den, 1);
+      den += __shfl_xor_sync(0xffffffffu, den, 2);
+      const float inv = 1.f / den;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+        pa[mt][nt >> 1][(nt & 1) * 2 + half] = pack_bf16x2(c[mt][nt][half * 2] * inv, c[mt][nt][half * 2 + 1] * inv);
+    }
+  }
+  __syncwarp();
+  // out = P v: B fragment = v[key pair 2i (+8)][dim g] -> two 16-bit loads per register
+  const uint8_t* vbase = rows + 2 * part_bytes + g * 2;
+  const int n_kb = (Tn + 15) >> 4;                      // key blocks of 16
+  for (int d0 = 0; d0 < D; d0 += 8) {
+    float o[2][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) o[mt][e] = 0.f;
+#pragma unroll
+    for (int kb = 0; kb < 2; ++kb) {
+      if (kb < n_kb) {
+        uint32_t b[2];
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          const int t0 = kb * 16 + r * 8 + i2;
+          const uint32_t lo = *reinterpret_cast<const uint16_t*>(vbase + min(t0, last) * pitch + d0 * 2);
+          const uint32_t hi = *reinterpret_cast<const uint16_t*>(vbase + min(t0 + 1, last) * pitch + d0 * 2);
+          b[r] = lo | (hi << 16);
+        }
+        mma_bf16_k16(o[0], pa[0][kb], b[0], b[1]);
+        if (n_mt > 1) mma_bf16_k16(o[1], pa[1][kb], b[0], b[1]);
+      }
+    }
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int tq = mt * 16 + half * 8 + g;
+        if (tq < Tn)
+          *reinterpret_cast<uint32_t*>(rows + tq * pitch + part_bytes + (d0 + i2) * 2) =
+              pack_bf16x2(o[mt][half * 2], o[mt][half * 2 + 1]);
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // bf16 production path (T <= 8, D % 8 == 0): shared-memory staged temporal attention.
 // A CTA owns TA_G token columns (β, s).  The T rows q|k|v of a column (3C contiguous bf16 each) arrive by
@@ -335,7 +491,7 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_kernel(const
                                                                           const float* __restrict__ sin_t,
                                                                           bf16* __restrict__ out, int64_t ldo,
                                                                           int64_t n_cols, int S, int H, int D,
-                                                                          float scale) {
+                                                                          float scale, int use_mma) {
   using namespace sm100;
   extern __shared__ __align__(128) uint8_t ta_smem[];
   const int C = H * D;
@@ -391,6 +547,13 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_kernel(const
     *ptr = x.raw;
   }
   __syncthreads();
+  if (use_mma) {
+    // ---- B + C on the tensor cores (mma.sync tiles, one warp per (column, head); see temporal_head_mma) ----
+    for (int idx = tid >> 5; idx < ng * H; idx += TA_THREADS / 32) {
+      const int h = idx % H, g = idx / H;
+      temporal_head_mma(ta_smem + g * TN * pitch + h * D * 2, pitch, C * 2, TN, D);
+    }
+  } else {
   // ---- B: scores + softmax; P[t_q][0..TN) -> first bytes of this thread's q slice ----
   if (tid < ng * H * TN) {
     const int tq = tid % TN, h = (tid / TN) % H, g = tid / (TN * H);
@@ -464,6 +627,7 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_kernel(const
       *reinterpret_cast<uint4*>(ta_smem + (g * TN + tq) * pitch + C * 2 + h * D * 2 + j * 16) = ov.raw;
     }
   }
+  }
   fence_async_smem();                                   // generic-proxy writes -> visible to the bulk stores
   __syncthreads();
   // ---- D: T output rows per column ----
@@ -497,7 +661,7 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_long_kernel(
                                                                                const float* __restrict__ sin_t,
                                                                                bf16* __restrict__ out, int64_t ldo,
                                                                                int64_t n_cols, int Tn, int S, int H,
-                                                                               int D, int HG, float scale) {
+                                                                               int D, int HG, float scale, int use_mma) {
   using namespace sm100;
   extern __shared__ __align__(128) uint8_t ta_smem[];
   const int C = H * D, W = HG * D;                      // elements per q (k, v) slice of the head group
@@ -555,6 +719,21 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_long_kernel(
     *ptr = x.raw;
   }
   __syncthreads();
+  if (use_mma) {
+    // ---- B + C on the tensor cores: one warp per head ----
+    for (int h = tid >> 5; h < HG; h += TA_THREADS / 32) temporal_head_mma(ta_smem + h * D * 2, pitch, part_bytes, Tn, D);
+    fence_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      for (int t = 0; t < Tn; ++t)
+        bulk_s2g(out + (row0 + (int64_t)t * S) * ldo + (int64_t)hg * W, ta_smem + t * pitch + part_bytes,
+                 (uint32_t)part_bytes);
+      bulk_commit();
+      bulk_wait_read0();
+    }
+    return;
+  }
+  // ---- scalar fallback (MDV2_TEMPORAL_LONG_SCALAR=1) ----
   // ---- B1: item = (head, t_q, t_k): one score, rounded to bf16 like the reference's q @ k^T ----
   const int Tp = (Tn + 3) & ~3;
   float* sc = reinterpret_cast<float*>(ta_smem + Tn * pitch + 16);      // [HG][Tn][Tp] scores, then probabilities
@@ -644,6 +823,7 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
         TA_G * H * Tn <= TA_THREADS) {
       const int64_t n_cols = (int64_t)B * S;
       const unsigned nb = (unsigned)((n_cols + TA_G - 1) / TA_G);
+      static const int short_mma = getenv("MDV2_TEMPORAL_MMA") != nullptr;       // A/B hook: tensor-core phases B + C
 #define TS_CASE(TT)                                                                                               \
   case TT: {                                                                                                      \
     static bool configured = false;                                                                               \
@@ -652,7 +832,7 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
       configured = true;                                                                                          \
     }                                                                                                             \
     temporal_attn_smem_kernel<TT><<<nb, TA_THREADS, smem, st>>>((const bf16*)qkv, ld, c, s, (bf16*)out, ldo, n_cols, \
-                                                               S, H, D, scale);                                   \
+                                                               S, H, D, scale, short_mma);                        \
   } break
       switch (Tn) {
         TS_CASE(1); TS_CASE(2); TS_CASE(3); TS_CASE(4); TS_CASE(5); TS_CASE(6); TS_CASE(7); TS_CASE(8);
@@ -665,8 +845,11 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
         ((uintptr_t)out % 16 == 0) && ((uintptr_t)c % 16 == 0) && ((uintptr_t)s % 16 == 0)) {
       // largest head group (a divisor of H, at most 8 heads) whose staged frames + score table leave room for three
       // CTAs per SM
+      static const bool scalar = getenv("MDV2_TEMPORAL_LONG_SCALAR") != nullptr;     // A/B hook
       const int Tp = (Tn + 3) & ~3;
-      auto smem_long = [&](int g) { return (size_t)Tn * (3 * g * D * 2 + TA_PAD) + 16 + (size_t)g * Tn * Tp * 4; };
+      auto smem_long = [&](int g) {
+        return (size_t)Tn * (3 * g * D * 2 + TA_PAD) + 16 + (scalar ? (size_t)g * Tn * Tp * 4 : 0);
+      };
       int HG = 0;
       for (int g = H < 8 ? H : 8; g >= 1; --g)
         if (H % g == 0 && smem_long(g) <= 75 * 1024) {
@@ -681,7 +864,7 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
           configured = true;
         }
         temporal_attn_smem_long_kernel<<<(unsigned)n_ctas, TA_THREADS, smem_long(HG), st>>>(
-            (const bf16*)qkv, ld, c, s, (bf16*)out, ldo, (int64_t)B * S, Tn, S, H, D, HG, scale);
+            (const bf16*)qkv, ld, c, s, (bf16*)out, ldo, (int64_t)B * S, Tn, S, H, D, HG, scale, scalar ? 0 : 1);
         MDV2_CHECK_LAUNCH("temporal_attention");
         return MDV2_OK;
       }
