@@ -62,3 +62,41 @@ def test_sequence_parallel_world2_matches_reference_golden(wl_name, xm):
     assert len(ret) == world
     for r in range(world):
         assert ret[r] < 2e-5, (r, ret[r])
+
+
+def _worker_brush(rank, world, port, fixture, skip_ca, sde, ret):
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for p in (root, os.path.join(root, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import spec_ops
+    from helpers import brushnet_inputs, build_brushnet, load_golden, rel_l2, sde_inputs, use_ops
+    from magicdrive_v2_b200 import sp
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(2)
+    try:
+        fix = load_golden(fixture)
+        model, wl, kw = build_brushnet(fix["workload"], skip_ca, sde=sde, enable_sequence_parallelism=True)
+        sp.set_sequence_parallel_group(dist.group.WORLD)
+        inp = (sde_inputs if sde else brushnet_inputs)(wl, kw, fix)
+        with use_ops(spec_ops):
+            out = model(**inp)
+        ret[rank] = rel_l2(out, fix["out"])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("fixture,skip_ca,sde", [("brushnet_tiny_9f_None_ca.pt", False, False),
+                                                 ("sde_tiny_9f_first0_noca.pt", True, True)])
+def test_brushnet_sequence_parallel_world2_matches_reference_golden(fixture, skip_ca, sde):
+    """The third (BrushNet / SDE-BrushNet) stream under sequence parallelism: every rank embeds and runs its S-slice of
+    the inpaint tokens; result vs the single-process golden of the REAL reference."""
+    world = 2
+    ret = mp.Manager().dict()
+    mp.spawn(_worker_brush, args=(world, _free_port(), fixture, skip_ca, sde, ret), nprocs=world, join=True)
+    assert len(ret) == world
+    for r in range(world):
+        assert ret[r] < 2e-5, (r, ret[r])
