@@ -72,3 +72,64 @@ def load_checkpoint(model, ckpt_path: str, model_name: str = "model", strict: bo
     logger.info("Missing keys: %s", res.missing_keys)
     logger.info("Unexpected keys: %s", res.unexpected_keys)
     return res
+
+
+def _as_state(src) -> dict:
+    if isinstance(src, dict):
+        return src
+    if os.path.isdir(src):
+        files = [f for f in sorted(os.listdir(src)) if f.endswith((".safetensors", ".bin", ".pt", ".pth"))]
+        if not files:
+            raise ValueError(f"no weight files under {src}")
+        state = {}
+        for f in files:
+            state.update(_load_file(os.path.join(src, f)))
+        return state
+    return _load_file(src)
+
+
+def _sub(state: dict, prefix: str) -> dict:
+    return {k[len(prefix):]: v for k, v in state.items() if k.startswith(prefix)}
+
+
+def _init_from_base(model, state: dict, spatial: str, temporal: str | None, what: str):
+    """Shared body of the two initialisers below: helper modules by name (non-strict), ``x_control_embedder`` from the
+    base ``x_embedder``, then the base model's block stack into BOTH the base and the control streams."""
+    res = model.load_state_dict(state, strict=False)
+    if getattr(model, "x_control_embedder", None) is not None:
+        model.x_control_embedder.load_state_dict(_sub(state, "x_embedder."))
+    skip_m, skip_u = ("base_blocks_", "control_blocks_"), tuple(p for p in (spatial, temporal) if p)
+    logger.info("1st, Load from %s with missing=%s, unexpected=%s", what,
+                [k for k in res.missing_keys if not k.startswith(skip_m)],
+                [k for k in res.unexpected_keys if not k.startswith(skip_u)])
+    sp_state = _sub(state, spatial + ".")
+    report = {}
+    report["base_s"] = model.base_blocks_s.load_state_dict(sp_state, strict=False)
+    n_ctrl = len(model.control_blocks_s)
+    ctrl_state = {k: v for k, v in sp_state.items() if int(k.split(".", 1)[0]) < n_ctrl}
+    report["control_s"] = model.control_blocks_s.load_state_dict(ctrl_state, strict=False)
+    if temporal is not None:
+        t_state = _sub(state, temporal + ".")
+        if model.base_blocks_t is not None:
+            report["base_t"] = model.base_blocks_t.load_state_dict(t_state, strict=False)
+        if model.control_blocks_t is not None:
+            ct_state = {k: v for k, v in t_state.items() if int(k.split(".", 1)[0]) < len(model.control_blocks_t)}
+            report["control_t"] = model.control_blocks_t.load_state_dict(ct_state, strict=False)
+    for name, r in report.items():
+        logger.info("Load %s from %s with missing=%s, unexpected=%s", name, what, r.missing_keys, r.unexpected_keys)
+    return model
+
+
+def load_from_stdit3_pretrained(model, from_pretrained):
+    """``magicdrive_stdit3.py:2473-2514`` at state-dict level: initialise from an OpenSora STDiT3 checkpoint (a local
+    file / directory or an already loaded state dict) — ``spatial_blocks.*`` / ``temporal_blocks.*`` go into both the
+    base and the control streams, the remaining modules load by name.  (The reference instantiates the base
+    ``STDiT3`` class to obtain its state dict; only the weights matter.)"""
+    return _init_from_base(model, _as_state(from_pretrained), "spatial_blocks", "temporal_blocks",
+                           from_pretrained if isinstance(from_pretrained, str) else "<state dict>")
+
+
+def load_from_pixart_pretrained(model, pretrained):
+    """``magicdrive_stdit3.py:2517-2552`` at state-dict level: initialise the spatial streams from a PixArt-XL/2
+    checkpoint (``blocks.*``; the control stream takes the first ``control_depth`` blocks)."""
+    return _init_from_base(model, _as_state(pretrained), "blocks", None, pretrained if isinstance(pretrained, str) else "<state dict>")

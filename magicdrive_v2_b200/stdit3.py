@@ -595,14 +595,19 @@ class MagicDriveSTDiT3(PreTrainedModel):
 
 
 def _build(cls, from_pretrained=None, force_huggingface=False, strict=True, **kwargs):
+    """Body shared by the three registry factories (magicdrive_stdit3.py:2554-2620)."""
     if from_pretrained is not None and not os.path.exists(from_pretrained):
         return cls.from_pretrained(from_pretrained, **kwargs)
-    kwargs.pop("from_pretrained_pixart", None)
+    from_pretrained_pixart = kwargs.pop("from_pretrained_pixart", None)
     config = MagicDriveSTDiT3Config(depth=28, hidden_size=1152, patch_size=(1, 2, 2), num_heads=16, **kwargs)
     model = cls(config)
-    if from_pretrained is not None:
-        from .checkpoint import load_checkpoint
-        load_checkpoint(model, from_pretrained, strict=strict)
+    from . import checkpoint
+    if from_pretrained is not None and force_huggingface:       # initialise from an STDiT3 base checkpoint
+        checkpoint.load_from_stdit3_pretrained(model, from_pretrained)
+    elif from_pretrained is not None:
+        checkpoint.load_checkpoint(model, from_pretrained, strict=strict)
+    elif from_pretrained_pixart is not None:
+        checkpoint.load_from_pixart_pretrained(model, from_pretrained_pixart)
     else:
         logger.info("Your model does not use any pre-trained model.")
     return model
