@@ -61,6 +61,10 @@ WORKLOADS = {
     "tiny_1f": dict(model=dict(hidden_size=384, depth=2, num_heads=6, control_depth=1,
                                caption_channels=64, model_max_length=24, map_size=400),
                     b=1, NC=6, t_pix=1, height=224, width=400, n_box=4, n_text=9),
+    # stage-1 image configuration (1x224x400 "noTemp" configs): no temporal blocks, un-pooled conditions
+    "tiny_1f_image": dict(model=dict(hidden_size=384, depth=2, num_heads=6, control_depth=1, video=False,
+                                     caption_channels=64, model_max_length=24, map_size=400),
+                          b=1, NC=6, t_pix=1, height=224, width=400, n_box=4, n_text=9),
     "tiny_9f": dict(model=dict(hidden_size=384, depth=2, num_heads=6, control_depth=1,
                                caption_channels=64, model_max_length=24, map_size=400),
                     b=1, NC=6, t_pix=9, height=224, width=400, n_box=4, n_text=9),

@@ -15,7 +15,7 @@ sys.path.insert(0, ROOT)
 from magicdrive_v2_b200 import synth  # noqa: E402
 from oracle import ref_loader  # noqa: E402
 
-CASES = [("tiny_1f", "ones"), ("tiny_9f", "ones"), ("tiny_9f", "first0"), ("tiny_9f", None),
+CASES = [("tiny_1f", "ones"), ("tiny_1f_image", "ones"), ("tiny_9f", "ones"), ("tiny_9f", "first0"), ("tiny_9f", None),
          ("tiny_d72", "first0")]
 
 

@@ -9,7 +9,7 @@ from helpers import build_model, load_golden, rel_l2
 from magicdrive_v2_b200 import synth
 
 pytestmark = pytest.mark.gpu
-CASES = [("tiny_1f", "ones"), ("tiny_9f", "ones"), ("tiny_9f", "first0"), ("tiny_9f", None),
+CASES = [("tiny_1f", "ones"), ("tiny_1f_image", "ones"), ("tiny_9f", "ones"), ("tiny_9f", "first0"), ("tiny_9f", None),
          ("tiny_d72", "first0")]
 
 
