@@ -238,6 +238,8 @@ class MagicDriveSTDiT3(PreTrainedModel):
                 mask = mask.repeat(y.shape[0] // mask.shape[0], 1)
             y_lens = [i + 1 for i in mask.sum(dim=1).tolist()]
             max_len = int(min(max(y_lens), y.shape[2]))
+            if drop_cond_mask is not None and not drop_cond_mask.all():        # on any drop this must be the maximum
+                assert max_len == y.shape[2]
             y = y.squeeze(1)[:, :max_len]
         else:
             y = y.squeeze(1)

@@ -25,6 +25,33 @@ def build_model(workload_name, seed=0, **extra_kw):
     return model, wl, kw
 
 
+def _drop_masks(wl, kw):
+    # full-length text mask: the reference asserts it whenever a sample is dropped (magicdrive_stdit3.py:873-874)
+    return dict(drop_cond_mask=torch.tensor([1.0, 0.0]),
+                drop_frame_mask=torch.tensor([[1.0] * 9, [1.0, 0, 1, 1, 0, 1, 1, 1, 0]]),
+                mask=torch.ones(1, kw["model_max_length"], dtype=torch.int64))
+
+
+# further configurations pinned to the real reference (oracle/make_golden_variants.py -> tests/golden/variant_*.pt):
+# name -> (workload, x_mask, constructor overrides, input overrides)
+VARIANTS = {
+    "ctrl_xview": ("tiny_9f", "first0", dict(control_skip_cross_view=False), None),   # control blocks with cross-view
+    "drop_masks": ("tiny_d72", "first0", {}, _drop_masks),        # dropped conditions / frames (null embeddings)
+}
+
+
+def variant_case(name):
+    """-> (workload, constructor kwargs, inputs) of a VARIANTS entry."""
+    wl_name, xm, kw_over, inp_over = VARIANTS[name]
+    wl = synth.WORKLOADS[wl_name]
+    kw = synth.model_kwargs(**wl["model"])
+    kw.update(kw_over)
+    inp = synth.make_inputs(wl, seed=0, x_mask=xm, kw=kw)
+    if inp_over is not None:
+        inp.update(inp_over(wl, kw))
+    return wl_name, kw, inp
+
+
 def load_golden(name):
     return torch.load(os.path.join(GOLDEN, name), weights_only=False)
 
