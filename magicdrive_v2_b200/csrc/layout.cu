@@ -673,11 +673,14 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_long_kernel(
   const int hg = (int)((int64_t)blockIdx.x - col * n_groups);
   const int64_t beta = col / S, s = col - beta * S;
   const int64_t row0 = beta * Tn * S + s;               // global row of frame 0; frame t is row0 + t·S
-  if (tid == 0) {
-    mbar_init(bar, 1);
-    fence_mbar_init();
-    mbar_expect_tx(bar, (uint32_t)(Tn * 3 * part_bytes));
-    for (int t = 0; t < Tn; ++t) {
+  if (tid < 32) {                                       // warp 0: lane t issues the three copies of frame t
+    if (tid == 0) {
+      mbar_init(bar, 1);
+      fence_mbar_init();
+      mbar_expect_tx(bar, (uint32_t)(Tn * 3 * part_bytes));
+    }
+    __syncwarp();
+    for (int t = tid; t < Tn; t += 32) {
       const bf16* src = qkv + (row0 + (int64_t)t * S) * ld + (int64_t)hg * W;
 #pragma unroll
       for (int part = 0; part < 3; ++part)
@@ -689,34 +692,36 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_long_kernel(
 
   const int vpp = W / 8;                                // 16-byte vectors per slice
   const int vph = D / 8;                                // ... per head
-  // ---- A: RoPE on q and k ----
-  for (int i = tid; i < Tn * 2 * vpp; i += TA_THREADS) {
-    const int v = i % vpp, part = (i / vpp) & 1, t = i / (2 * vpp);
+  // ---- A: RoPE on q and k: a thread owns one 16-byte vector position (part, v) and walks the frames ----
+  for (int pv = tid; pv < 2 * vpp; pv += TA_THREADS) {
+    const int v = pv % vpp, part = pv / vpp;
     const int d0 = (v % vph) * 8;
-    uint4* ptr = reinterpret_cast<uint4*>(ta_smem + t * pitch + part * part_bytes + v * 16);
-    Vec16<bf16> x;
-    x.raw = *ptr;
-    float f[8], o[8];
-    x.unpack(f);
-    const float4 c0 = *reinterpret_cast<const float4*>(cos_t + t * D + d0);
-    const float4 c1 = *reinterpret_cast<const float4*>(cos_t + t * D + d0 + 4);
-    const float4 s0 = *reinterpret_cast<const float4*>(sin_t + t * D + d0);
-    const float4 s1 = *reinterpret_cast<const float4*>(sin_t + t * D + d0 + 4);
-    const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
-    const float sn[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-#pragma unroll
-    for (int e = 0; e < 8; e += 2) {
-      o[e] = f[e] * cs[e] - f[e + 1] * sn[e];
-      o[e + 1] = f[e + 1] * cs[e + 1] + f[e] * sn[e + 1];
-    }
-    x.pack(o);
-    if (part == 0) {                                    // q = (rope(q) in bf16) * scale, in bf16
+    for (int t = 0; t < Tn; ++t) {
+      uint4* ptr = reinterpret_cast<uint4*>(ta_smem + t * pitch + part * part_bytes + v * 16);
+      Vec16<bf16> x;
+      x.raw = *ptr;
+      float f[8], o[8];
       x.unpack(f);
+      const float4 c0 = *reinterpret_cast<const float4*>(cos_t + t * D + d0);
+      const float4 c1 = *reinterpret_cast<const float4*>(cos_t + t * D + d0 + 4);
+      const float4 s0 = *reinterpret_cast<const float4*>(sin_t + t * D + d0);
+      const float4 s1 = *reinterpret_cast<const float4*>(sin_t + t * D + d0 + 4);
+      const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+      const float sn[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
 #pragma unroll
-      for (int e = 0; e < 8; ++e) f[e] *= scale;
-      x.pack(f);
+      for (int e = 0; e < 8; e += 2) {
+        o[e] = f[e] * cs[e] - f[e + 1] * sn[e];
+        o[e + 1] = f[e + 1] * cs[e + 1] + f[e] * sn[e + 1];
+      }
+      x.pack(o);
+      if (part == 0) {                                  // q = (rope(q) in bf16) * scale, in bf16
+        x.unpack(f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] *= scale;
+        x.pack(f);
+      }
+      *ptr = x.raw;
     }
-    *ptr = x.raw;
   }
   __syncthreads();
   if (use_mma) {
@@ -724,12 +729,12 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_long_kernel(
     for (int h = tid >> 5; h < HG; h += TA_THREADS / 32) temporal_head_mma(ta_smem + h * D * 2, pitch, part_bytes, Tn, D);
     fence_async_smem();
     __syncthreads();
-    if (tid == 0) {
-      for (int t = 0; t < Tn; ++t)
+    if (tid < 32) {                                     // lane t stores frame t (a bulk group is per thread)
+      for (int t = tid; t < Tn; t += 32)
         bulk_s2g(out + (row0 + (int64_t)t * S) * ldo + (int64_t)hg * W, ta_smem + t * pitch + part_bytes,
                  (uint32_t)part_bytes);
       bulk_commit();
-      bulk_wait_read0();
+      bulk_wait_read0();                                // shared memory must outlive the reads
     }
     return;
   }
