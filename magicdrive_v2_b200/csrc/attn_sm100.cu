@@ -22,16 +22,12 @@
 // and the bf16 outputs are summed like the reference's gather+sum (stdit3.py:311-322).
 #include <cstdlib>
 
-#include "common.cuh"
-#include "sm100_ptx.cuh"
+#include "attn_common.cuh"
 
 using namespace sm100;
-
-int mdv2_make_tmap_3d_heads(CUtensorMap* out, const void* ptr, uint64_t rows, uint32_t H, uint32_t D, uint64_t ld,
-                            uint32_t box_rows);
+using namespace attn;
 
 namespace {
-constexpr int BMQ = 128;          // query rows per tile
 // CTA shape.  128-key tiles (self / cross-view attention): two query tiles per CTA, 11 warps (TMA, MMA of tile 0,
 // 8 softmax warps, MMA of tile 1), all 512 TMEM columns: S_t (and P_t over it) at 128·t, O_t at 256 + 128·t,
 // Q_t (bf16 pairs, DP/2 <= 40 columns) at 336 + 128·t in the gaps behind O_t.
@@ -64,53 +60,6 @@ struct ACfg {
   static_assert(!ALIAS_Q || Q_BYTES == KV_BYTES, "Q tile must fit a K/V stage");
 };
 
-struct AParams {
-  bf16* out;
-  int64_t ldo;
-  int Lq, Lk, H, D, n_sets;
-  float scale_log2;
-  const int32_t* kv_map;
-  // sequence parallelism: the normalised output rows of the LAST K/V set go straight to the rank that owns the row
-  // (peer-mapped [n_seq·rows_per_rank, peer_ld] buffers, this rank's head group at column peer_col); `out` then only
-  // carries the running sum of earlier sets.  n_peer == 0: everything goes to `out`.
-  bf16* peer_out[8];
-  int n_peer, rows_per_rank, peer_col;
-  int64_t peer_ld;
-  long long* trace;        // debug timeline (tools/attn_trace.py) or nullptr
-  int dbg;                 // debug switches (MDV2_ATTN_DBG): bit 0 swaps the TMA / MMA warps, bit 1 disables the ping-pong
-};
-
-constexpr int TRACE_STEPS = 96, TRACE_EV = 12;
-__device__ __forceinline__ long long clk64() {
-  long long t;
-  asm volatile("mov.u64 %0, %%clock64;" : "=l"(t)::"memory");
-  return t;
-}
-
-__device__ __forceinline__ float ex2(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
-// 2^x for a pair on the FMA pipe (no MUFU): x = n + f, n = round(x), f in [-1/2, 1/2]; 2^f by the degree-3 minimax
-// polynomial (max rel. error 7.5e-5 = 2^-13.7, far below the bf16 rounding of P), 2^n added into the exponent field.
-__device__ __forceinline__ float2 ex2_poly2(float2 x) {
-  const float MAGIC = 12582912.f;                        // 1.5 * 2^23: x + MAGIC rounds x to an integer in the mantissa
-  x.x = fmaxf(x.x, -126.f);
-  x.y = fmaxf(x.y, -126.f);
-  const float2 t = fadd2(x, make_float2(MAGIC, MAGIC));
-  const float2 nf = fadd2(t, make_float2(-MAGIC, -MAGIC));
-  const float2 f = ffma2(nf, make_float2(-1.f, -1.f), x);
-  float2 q = ffma2(f, make_float2(0.05517202615737915f, 0.05517202615737915f),
-                   make_float2(0.2426111400127411f, 0.2426111400127411f));
-  q = ffma2(q, f, make_float2(0.693260908126831f, 0.693260908126831f));
-  q = ffma2(q, f, make_float2(0.9999280571937561f, 0.9999280571937561f));
-  float2 r;
-  r.x = __uint_as_float(__float_as_uint(q.x) + (__float_as_uint(t.x) << 23));
-  r.y = __uint_as_float(__float_as_uint(q.y) + (__float_as_uint(t.y) << 23));
-  return r;
-}
 // Measured (tools/probes/pipe_probe.cu, clk per warp instruction and SM sub-partition): MUFU.EX2 8, FFMA2 3, FADD2 /
 // FMNMX3 / F2FP 2, FFMA / FADD 1.  The packed forms cost pipe time but save issue slots, and the loop below is
 // bound by the MUFU pipe (64 exponentials x 2 resident warps x 8 clk ~ the 1000 clk a half-step takes): a scalar
@@ -124,7 +73,6 @@ __device__ __forceinline__ float2 ex2_poly2(float2 x) {
 // barrier per half-step): each chain got 30 % shorter but paid 140 clk of exchange, 725 vs 747 TF/s, removed
 // (profiles/attn_trace_rowsplit_r01.txt).
 // pair index (0..BNK/2) -> evaluated by the polynomial?  PF of every 8 pairs, spread evenly.
-__host__ __device__ constexpr bool poly_pair(int pair, int PF) { return ((pair % 8) * PF) / 8 != (((pair % 8) + 1) * PF) / 8; }
 
 template <int DP, int BNK, int PF = 0, bool TRACE = false>
 __global__ void __launch_bounds__(AShape<BNK>::NTHREADS, AShape<BNK>::CTAS_PER_SM)
@@ -545,6 +493,9 @@ int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap&
 // debug hook (not part of include/mdv2.h): device buffer of 10 x TRACE_STEPS x TRACE_EV int64 clock samples
 extern "C" void mdv2_debug_attn_trace(void* buf) { g_attn_trace = (long long*)buf; }
 
+int mdv2_attention_fast_launch(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p,
+                               int n_seq, int D, bool trace, cudaStream_t st);
+
 bool mdv2_attention_sm100_supported(int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int Lq, int Lk, int H, int D,
                                     int n_sets) {
   if (D != 64 && D != 72) return false;
@@ -600,6 +551,11 @@ int mdv2_attention_sm100(const void* q, int64_t ldq, const void* k, int64_t ldk,
     const char* e = getenv("MDV2_ATTN_PF");
     return e ? atoi(e) : ATTN_PF_DEFAULT;
   }();
+  static const int fast = [] {                           // MDV2_ATTN_FAST=0: the exact online-softmax kernel below
+    const char* e = getenv("MDV2_ATTN_FAST");
+    return e ? atoi(e) : 1;
+  }();
+  if (bnk == 128 && fast) return mdv2_attention_fast_launch(tq, tk, tv, p, n_seq, D, g_attn_trace != nullptr, st);
   if (D == 72 && bnk == 128 && g_attn_trace) {
     if (pf == 0) return launch_attn<80, 128, 0, true>(tq, tk, tv, p, n_seq, st);
     return launch_attn<80, 128, ATTN_PF_DEFAULT ? ATTN_PF_DEFAULT : 3, true>(tq, tk, tv, p, n_seq, st);

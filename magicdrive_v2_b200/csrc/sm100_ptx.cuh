@@ -299,6 +299,15 @@ __device__ __forceinline__ void tmem_ld_x32(uint32_t taddr, uint32_t* r) {
       : "r"(taddr));
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// the same for a load that was issued long before (software pipelining): the destination registers pass THROUGH the
+// wait, so no instruction that reads them can be scheduled ahead of it
+#define MDV2_RW8(r, o) "+r"(r[o]), "+r"(r[o + 1]), "+r"(r[o + 2]), "+r"(r[o + 3]), "+r"(r[o + 4]), "+r"(r[o + 5]), "+r"(r[o + 6]), "+r"(r[o + 7])
+__device__ __forceinline__ void tmem_ld_wait_x32(uint32_t* r) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : MDV2_RW8(r, 0), MDV2_RW8(r, 8), MDV2_RW8(r, 16), MDV2_RW8(r, 24)
+               :
+               : "memory");
+}
 
 // registers -> TMEM (used to hand the bf16 probabilities P to the PV MMA)
 __device__ __forceinline__ void tmem_st_x8(uint32_t taddr, const uint32_t* r) {

@@ -72,6 +72,17 @@ WORKLOADS = {
     "tiny_d72": dict(model=dict(hidden_size=576, depth=2, num_heads=8, control_depth=1,
                                 caption_channels=64, model_max_length=24, map_size=400),
                      b=2, NC=6, t_pix=9, height=224, width=400, n_box=4, n_text=9),
+    # long clip at toy width: 65 pixel frames -> T = 17 latent frames (the 8 < T <= 32 temporal kernel at model level)
+    "tiny_65f": dict(model=dict(hidden_size=384, depth=2, num_heads=6, control_depth=1,
+                                caption_channels=64, model_max_length=24, map_size=400),
+                     b=1, NC=6, t_pix=65, height=224, width=400, n_box=4, n_text=9),
+    # D = 72 heads with the XL condition length: 40 text + 20 box + cam + frame tokens = 62 keys in cross-attention
+    "tiny_l62": dict(model=dict(hidden_size=576, depth=2, num_heads=8, control_depth=1,
+                                caption_channels=64, model_max_length=48, map_size=400),
+                     b=1, NC=6, t_pix=9, height=224, width=400, n_box=20, n_text=40),
+    # cfg2 at b = 1 (one CFG half): the XL-depth golden of the real reference (oracle/make_golden_xl.py)
+    "xl_17f_224x400_b1": dict(model=dict(), b=1, NC=6, t_pix=17, height=224, width=400,
+                              n_box=20, n_text=40),
     # cfg2: XL/2, 6 views x 17 frames x 224x400, CFG batch-doubled (b=2)
     "xl_17f_224x400": dict(model=dict(), b=2, NC=6, t_pix=17, height=224, width=400,
                            n_box=20, n_text=40),

@@ -1,0 +1,176 @@
+// softmax_probe.cu — what one SM sub-partition can do on the attention softmax inner loop (sm_100a), without the
+// tensor-core pipeline around it: W warps per sub-partition each run `iters` chunks of 32 scores held in registers
+// (p = 2^(s·c − m), row sum, running max, bf16 pack), in the variants the attention kernel could use.
+//   clk per score per sub-partition = elapsed / (iters · 32 · W)          (MUFU.EX2 bound: 8)
+// Variants: PF = polynomial pairs per 8 (FMA-pipe 2^x instead of MUFU), MAXK = track the chunk maximum or not,
+//           ORDER 0 = fused loop as in the kernel, 1 = all exponentials first, then sums + packs (more distance between
+//           a MUFU and its consumers).
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(*reinterpret_cast<uint64_t*>(&a)), "l"(*reinterpret_cast<uint64_t*>(&b)), "l"(*reinterpret_cast<uint64_t*>(&c)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(*reinterpret_cast<uint64_t*>(&a)), "l"(*reinterpret_cast<uint64_t*>(&b)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float2 ex2_poly2(float2 x) {
+  const float MAGIC = 12582912.f;
+  x.x = fmaxf(x.x, -126.f);
+  x.y = fmaxf(x.y, -126.f);
+  const float2 t = fadd2(x, make_float2(MAGIC, MAGIC));
+  const float2 nf = fadd2(t, make_float2(-MAGIC, -MAGIC));
+  const float2 f = ffma2(nf, make_float2(-1.f, -1.f), x);
+  float2 q = ffma2(f, make_float2(0.05517202615737915f, 0.05517202615737915f), make_float2(0.2426111400127411f, 0.2426111400127411f));
+  q = ffma2(q, f, make_float2(0.693260908126831f, 0.693260908126831f));
+  q = ffma2(q, f, make_float2(0.9999280571937561f, 0.9999280571937561f));
+  float2 r;
+  r.x = __uint_as_float(__float_as_uint(q.x) + (__float_as_uint(t.x) << 23));
+  r.y = __uint_as_float(__float_as_uint(q.y) + (__float_as_uint(t.y) << 23));
+  return r;
+}
+// cheaper variant: no clamp (caller guarantees x >= -126 is irrelevant: flush handled by the shift wrap for P ~ 0?
+// NO — kept only as a cost probe), degree-2 polynomial
+__device__ __forceinline__ float2 ex2_poly2_lite(float2 x) {
+  const float MAGIC = 12582912.f;
+  const float2 t = fadd2(x, make_float2(MAGIC, MAGIC));
+  const float2 nf = fadd2(t, make_float2(-MAGIC, -MAGIC));
+  const float2 f = ffma2(nf, make_float2(-1.f, -1.f), x);
+  float2 q = ffma2(f, make_float2(0.2426111400127411f, 0.2426111400127411f), make_float2(0.693260908126831f, 0.693260908126831f));
+  q = ffma2(q, f, make_float2(0.9999280571937561f, 0.9999280571937561f));
+  float2 r;
+  r.x = __uint_as_float(__float_as_uint(q.x) + (__float_as_uint(t.x) << 23));
+  r.y = __uint_as_float(__float_as_uint(q.y) + (__float_as_uint(t.y) << 23));
+  return r;
+}
+__host__ __device__ constexpr bool poly_pair(int pair, int PF) { return ((pair % 8) * PF) / 8 != (((pair % 8) + 1) * PF) / 8; }
+
+constexpr int CH = 32;
+
+template <int PF, int MAXK, int ORDER>
+__global__ void __launch_bounds__(512, 1) k(float* out, int iters, long long* clk, float c, float moff) {
+  // scores come from / probabilities go to shared memory (8 LDS.128 + 4 STS.128 per chunk: the stand-in for the
+  // kernel's tcgen05.ld / tcgen05.st; an empty asm on the registers does not stop nvcc from hoisting the loop body)
+  extern __shared__ uint4 sm[];
+  const int nt = blockDim.x, tid = threadIdx.x;
+  uint4* s_in = sm;                 // [8][nt]
+  uint4* p_out = sm + 8 * nt;       // [4][nt]
+  for (int i = 0; i < 8; ++i) {
+    uint4 v;
+    v.x = __float_as_uint(-(float)((tid * 7 + i * 12) % 13)); v.y = __float_as_uint(-(float)((tid * 7 + i * 12 + 3) % 13));
+    v.z = __float_as_uint(-(float)((tid * 7 + i * 12 + 6) % 13)); v.w = __float_as_uint(-(float)((tid * 7 + i * 12 + 9) % 13));
+    s_in[i * nt + tid] = v;
+  }
+  float l_run = 0.f, m_run = -1e30f;
+  __syncthreads();
+  long long t0 = clock64();
+  for (int it = 0; it < iters; ++it) {
+    uint32_t s[CH];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      uint4 v;
+      asm volatile("ld.volatile.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                   : "r"((uint32_t)__cvta_generic_to_shared(&s_in[i * nt + tid])));
+      s[4 * i] = v.x; s[4 * i + 1] = v.y; s[4 * i + 2] = v.z; s[4 * i + 3] = v.w;
+    }
+    uint32_t pk[CH / 2];
+    const float2 c2 = make_float2(c, c), nm2 = make_float2(-moff, -moff);
+    float2 la = make_float2(0.f, 0.f), lb = make_float2(0.f, 0.f);
+    float mx0 = -INFINITY, mx1 = -INFINITY;
+    if (ORDER == 0) {
+#pragma unroll
+      for (int i = 0; i < CH; i += 4) {
+        const float s0 = __uint_as_float(s[i]), s1 = __uint_as_float(s[i + 1]);
+        const float s2 = __uint_as_float(s[i + 2]), s3 = __uint_as_float(s[i + 3]);
+        if (MAXK) { mx0 = fmax3(mx0, s0, s1); mx1 = fmax3(mx1, s2, s3); }
+        const float2 x01 = ffma2(make_float2(s0, s1), c2, nm2);
+        const float2 x23 = ffma2(make_float2(s2, s3), c2, nm2);
+        float2 e01, e23;
+        if (poly_pair(i / 2, PF)) e01 = ex2_poly2(x01); else e01 = make_float2(ex2(x01.x), ex2(x01.y));
+        if (poly_pair(i / 2 + 1, PF)) e23 = ex2_poly2(x23); else e23 = make_float2(ex2(x23.x), ex2(x23.y));
+        la = fadd2(la, e01);
+        lb = fadd2(lb, e23);
+        __nv_bfloat162 b01 = __floats2bfloat162_rn(e01.x, e01.y), b23 = __floats2bfloat162_rn(e23.x, e23.y);
+        pk[i / 2] = *reinterpret_cast<uint32_t*>(&b01);
+        pk[i / 2 + 1] = *reinterpret_cast<uint32_t*>(&b23);
+      }
+    } else {
+      float2 e[CH / 2];
+#pragma unroll
+      for (int i = 0; i < CH; i += 2) {
+        const float s0 = __uint_as_float(s[i]), s1 = __uint_as_float(s[i + 1]);
+        if (MAXK) { if ((i / 2) & 1) mx1 = fmax3(mx1, s0, s1); else mx0 = fmax3(mx0, s0, s1); }
+        const float2 x = ffma2(make_float2(s0, s1), c2, nm2);
+        if (poly_pair(i / 2, PF)) e[i / 2] = ORDER == 2 ? ex2_poly2_lite(x) : ex2_poly2(x);
+        else e[i / 2] = make_float2(ex2(x.x), ex2(x.y));
+      }
+#pragma unroll
+      for (int i = 0; i < CH / 2; ++i) asm volatile("" : "+f"(e[i].x), "+f"(e[i].y));   // keep the two phases apart
+#pragma unroll
+      for (int i = 0; i < CH / 2; ++i) {
+        if (i & 1) lb = fadd2(lb, e[i]); else la = fadd2(la, e[i]);
+        __nv_bfloat162 b = __floats2bfloat162_rn(e[i].x, e[i].y);
+        pk[i] = *reinterpret_cast<uint32_t*>(&b);
+      }
+    }
+    l_run += (la.x + la.y) + (lb.x + lb.y);
+    if (MAXK) m_run = fmaxf(m_run, fmaxf(mx0, mx1));
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      asm volatile("st.volatile.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"((uint32_t)__cvta_generic_to_shared(&p_out[i * nt + tid])),
+                   "r"(pk[4 * i]), "r"(pk[4 * i + 1]), "r"(pk[4 * i + 2]), "r"(pk[4 * i + 3]) : "memory");
+  }
+  long long t1 = clock64();
+  out[blockIdx.x * blockDim.x + threadIdx.x] = l_run + m_run;
+  if (threadIdx.x == 0 && blockIdx.x == 0) *clk = t1 - t0;
+}
+
+template <int PF, int MAXK, int ORDER>
+void run(const char* name, float* out, long long* clk) {
+  const int iters = 4000;
+  for (int W : {1, 2, 3, 4}) {
+    for (int rep = 0; rep < 2; ++rep) {
+      k<PF, MAXK, ORDER><<<1, W * 128, 12 * W * 128 * 16>>>(out, iters, clk, 0.17f, -1.0f);
+      cudaDeviceSynchronize();
+    }
+    printf("%-44s W=%d per sub-partition: %6.2f clk per score per sub-partition (%7.1f clk per 32-score chunk per warp)\n",
+           name, W, (double)*clk / ((double)iters * CH * W), (double)*clk / iters);
+  }
+}
+
+int main() {
+  float* out; long long* clk;
+#define SETSM(...) cudaFuncSetAttribute(k<__VA_ARGS__>, cudaFuncAttributeMaxDynamicSharedMemorySize, 12 * 512 * 16)
+  SETSM(0, 1, 0); SETSM(0, 0, 0); SETSM(2, 1, 0); SETSM(3, 1, 0); SETSM(4, 1, 0); SETSM(0, 1, 1); SETSM(2, 1, 1); SETSM(3, 1, 1); SETSM(4, 1, 1); SETSM(4, 1, 2); SETSM(6, 1, 2);
+  cudaMalloc(&out, 1 << 20); cudaMallocManaged(&clk, 8);
+  run<0, 1, 0>("fused loop, PF=0, max", out, clk);
+  run<0, 0, 0>("fused loop, PF=0, no max", out, clk);
+  run<2, 1, 0>("fused loop, PF=2, max", out, clk);
+  run<3, 1, 0>("fused loop, PF=3, max", out, clk);
+  run<4, 1, 0>("fused loop, PF=4, max", out, clk);
+  run<0, 1, 1>("two-phase, PF=0, max", out, clk);
+  run<2, 1, 1>("two-phase, PF=2, max", out, clk);
+  run<3, 1, 1>("two-phase, PF=3, max", out, clk);
+  run<4, 1, 1>("two-phase, PF=4, max", out, clk);
+  run<4, 1, 2>("two-phase, PF=4 lite poly (deg 2, no clamp), max", out, clk);
+  run<6, 1, 2>("two-phase, PF=6 lite poly, max", out, clk);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { printf("CUDA error: %s\n", cudaGetErrorString(e)); return 1; }
+  return 0;
+}
