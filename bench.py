@@ -16,10 +16,17 @@ Timed regions:
   e2e   : the same forward called with HOST (pinned) inputs: H2D of every input tensor and D2H of the
           predicted velocity inside the timed region.
   roofline / kernels : one extra instrumented step with a CUDA-event pair around every libmdv2 call.
-  cpu_baseline : the CPU oracle (port of the reference forward, oracle/stdit3_oracle.py) on the host
-          cores, on a bounded sample of the same workload (rank 0, N = 1 only).
-`--impl reference` times only that CPU leg (the reference is pure PyTorch and cannot travel to the
-GPU box; its restatement, pinned to the reference's golden vectors, is what runs).
+  cpu_baseline : the reference's CPU forward on the host cores, on a bounded sample of the same workload
+          (rank 0, N = 1 only) and EXTRAPOLATED to the full step ("extrapolated": true).  kind "reference" = the
+          UNMODIFIED reference module from oracle/_ref (oracle/populate_ref.py ships its 17 Python files with the
+          snapshot) where its eager attention fits the host (224x400); kind "port" = the CPU oracle
+          (oracle/stdit3_oracle.py, same arithmetic, attention walked in slices) at 848x1600, where the
+          reference's [6, 16, 5600, 5600] fp32 score tensors (3 x 12 GB live per attention) do not.
+`--impl reference` times only that CPU leg.  `--cpu-full-reference` runs ONE fully measured forward of the real
+reference at full depth (xl_17f_224x400, b = 1: minutes) — kept out of the default run, its line is committed
+under profiles/.
+At N > 1 the line carries "sp_parity_rel_l2": the sequence-parallel output of the timed configuration against a
+non-parallel forward of the same inputs and weights on rank 0.
 """
 import argparse
 import json
@@ -72,6 +79,14 @@ def algorithmic_flops(b, NC, T, S, L, C=1152, depth=28, cdepth=13, mlp=4):
 # ---------------------------------------------------------------------------------------------------
 # CPU leg (oracle port), shared by cpu_baseline and --impl reference
 # ---------------------------------------------------------------------------------------------------
+def _reference_available():
+    try:
+        from oracle import ref_loader
+        return ref_loader.available()
+    except Exception:  # noqa: BLE001
+        return False
+
+
 class CpuSample:
     """Bounded sample of the workload for the host cores: b = 1, ONE latent frame (t_pix = 1), ONE block of
     each of the four kinds at the full XL width and the full per-frame token count S.  The full step is
@@ -87,27 +102,77 @@ class CpuSample:
         self.full_b = wl["b"]
         wl.update(b=1, t_pix=1)
         kw = synth.model_kwargs(**dict(wl["model"], depth=1, control_depth=1))
+        S = workload_config(wl_name, 1)["tokens_per_frame"]
+        # the reference materialises [NC, heads, S, S] scores (fp32 + two copies) per spatial attention
+        score_gb = 3 * wl["NC"] * 16 * S * S * 4 / 1e9
+        self.kind = "reference" if _reference_available() and score_gb < 16 else "port"
         torch.manual_seed(0)
-        model = MagicDriveSTDiT3(MagicDriveSTDiT3Config(**kw)).eval()     # container of reference-layout weights
-        synth.fill_params(model, seed=0)
-        self.sd = {k: v.clone() for k, v in model.state_dict().items()}
+        if self.kind == "reference":
+            from oracle import ref_loader
+            self.ref = synth.fill_params(ref_loader.build_reference_model(kw).eval(), seed=0)
+            self.timers = {}
+            for kind in N_BLOCKS:
+                for blk in (getattr(self.ref, kind, None) or []):
+                    blk.register_forward_pre_hook(lambda m, a, k=kind: self.timers.__setitem__("_t0", time.perf_counter()))
+                    blk.register_forward_hook(lambda m, a, o, k=kind: self.timers.__setitem__(
+                        k, self.timers.get(k, 0.0) + time.perf_counter() - self.timers["_t0"]))
+        else:
+            model = MagicDriveSTDiT3(MagicDriveSTDiT3Config(**kw)).eval()     # container of reference-layout weights
+            synth.fill_params(model, seed=0)
+            self.sd = {k: v.clone() for k, v in model.state_dict().items()}
         self.kw = kw
         self.inp = synth.make_inputs(wl, seed=0, x_mask="ones", kw=kw)
-        self.desc = (f"oracle port, fp32: b=1 of {self.full_b}, 1 of {self.full_T} latent frames, 1 block of each "
+        who = ("the unmodified reference module (oracle/_ref)" if self.kind == "reference" else
+               "oracle port (the reference's eager attention does not fit the host at this S)")
+        self.desc = (f"{who}, fp32: b=1 of {self.full_b}, 1 of {self.full_T} latent frames, 1 block of each "
                      f"kind (base_s/ctrl_s/base_t/ctrl_t) of 28/13/28/13 at full width and S; step time = "
                      f"{self.full_b * self.full_T} x (other + sum n_kind·t_kind)")
 
     def step(self):
         """-> estimated seconds for the FULL step on these host cores."""
-        from oracle import stdit3_oracle
-        timers = {}
         t0 = time.perf_counter()
-        stdit3_oracle.forward(self.sd, self.kw, timers=timers, **self.inp)
+        if self.kind == "reference":
+            self.timers.clear()
+            with torch.no_grad():
+                self.ref(**self.inp)
+            timers = {k: v for k, v in self.timers.items() if k != "_t0"}
+        else:
+            from oracle import stdit3_oracle
+            timers = {}
+            stdit3_oracle.forward(self.sd, self.kw, timers=timers, **self.inp)
         total = time.perf_counter() - t0
         blocks = sum(timers.values())
         other = total - blocks
         est = other + sum(N_BLOCKS[k] * timers.get(k, 0.0) for k in N_BLOCKS)
         return est * self.full_b * self.full_T, total
+
+    def record(self, est, wall, cores):
+        return dict(value=1.0 / est, unit=UNIT, cores=cores, kind=self.kind, extrapolated=True, sample=self.desc,
+                    sample_wall_s=wall)
+
+
+def run_full_reference(args):
+    """ONE fully measured forward of the real reference at full depth on the host cores (xl_17f_224x400 at b = 1)."""
+    from magicdrive_v2_b200 import synth
+    from oracle import ref_loader
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    wl = synth.WORKLOADS["xl_17f_224x400_b1"]
+    kw = synth.model_kwargs(**wl["model"])
+    torch.manual_seed(0)
+    ref = synth.fill_params(ref_loader.build_reference_model(kw).eval(), seed=0)
+    inp = synth.make_inputs(wl, seed=0, x_mask="first0", kw=kw)
+    t0 = time.perf_counter()
+    with torch.no_grad():
+        out = ref(**inp)
+    dt = time.perf_counter() - t0
+    cfg = workload_config("xl_17f_224x400_b1", 1)
+    print(json.dumps(dict(metric=METRIC, value=1.0 / dt, unit=UNIT, impl="reference", n_gpus=0, steps=1, warmup=0,
+                          ms_per_step=dt * 1e3, higher_is_better=True, dtype="fp32", data="synthetic", config=cfg,
+                          cpu_baseline=dict(value=1.0 / dt, unit=UNIT, cores=cores, kind="reference",
+                                            extrapolated=False,
+                                            sample="one whole forward of the unmodified reference, full depth"),
+                          out_abs_mean=out.abs().mean().item())), flush=True)
 
 
 def run_reference_arm(args, rank):
@@ -130,8 +195,7 @@ def run_reference_arm(args, rank):
                 warmup=args.warmup, ms_per_step=est * 1e3, higher_is_better=True, scaling="strong",
                 vs_baseline=None, dtype="fp32", data="synthetic",
                 config=workload_config(args.workload, 1),
-                cpu_baseline=dict(value=val, unit=UNIT, cores=cores, kind="port", sample=sample.desc,
-                                  sample_wall_s=wall / max(1, args.steps)),
+                cpu_baseline=sample.record(est, wall / max(1, args.steps), cores),
                 e2e=dict(value=val, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 gpu_launches=0)
     print(json.dumps(line), flush=True)
@@ -266,6 +330,26 @@ def measure(wl_name, args, rank, world, device, pk, do_profile=True):
     def step():
         return model(**inp)
 
+    sp_parity = None
+    if dist_on:
+        # parity where the driver can see it (SP == non-SP at equal force_pad_h_for_sp_size): the
+        # sequence-parallel output of this very configuration against a non-parallel forward of the same inputs and
+        # weights on rank 0 (it fits one GPU: it is the N = 1 workload)
+        out_sp = step().float()
+        torch.cuda.synchronize()
+        if rank == 0:
+            model.enable_sequence_parallelism = False
+            model._ws = None
+            out_1 = model(**inp).float()
+            sp_parity = ((out_sp - out_1).norm() / out_1.norm()).item()
+            assert torch.isfinite(out_sp).all() and torch.isfinite(out_1).all()
+            del out_1
+            model.enable_sequence_parallelism = True
+            model._ws = None
+            torch.cuda.empty_cache()
+        del out_sp
+        import torch.distributed as dist
+        dist.barrier()
     for _ in range(args.warmup):
         step()
     torch.cuda.synchronize()
@@ -284,7 +368,11 @@ def measure(wl_name, args, rank, world, device, pk, do_profile=True):
     model.clear_condition_cache()
 
     # end to end: host (pinned) inputs -> H2D -> forward -> D2H of the velocity
-    out_host = torch.empty(step().shape, dtype=torch.float32).pin_memory()
+    o_ = step()
+    finite = bool(torch.isfinite(o_).all().item())
+    assert finite, "the timed configuration produced non-finite values"
+    out_host = torch.empty(o_.shape, dtype=torch.float32).pin_memory()
+    del o_
 
     def e2e_step():
         d = to_dev(host, device)
@@ -308,7 +396,7 @@ def measure(wl_name, args, rank, world, device, pk, do_profile=True):
     del model
     torch.cuda.empty_cache()
     return dict(ms_step=ms_step, ms_cached=ms_cached, ms_e2e=ms_e2e, h2d=h2d, d2h=d2h, launches=launches,
-                clocks=clocks, kernels=kernels, wl=wl)
+                clocks=clocks, kernels=kernels, wl=wl, sp_parity=sp_parity, finite=finite)
 
 
 def kernel_table(kernels, pk):
@@ -316,7 +404,8 @@ def kernel_table(kernels, pk):
     rows = {}
     for name, k in sorted(kernels.items(), key=lambda kv: -kv[1]["ms"]):
         # cross-attention to ~62 condition tokens has ~62 FLOP per byte (ridge: > 200): judged on HBM bytes
-        tensor = k["flops"] > 0 and ("gemm" in name or ("attention_s" in name and "[cross]" not in name))
+        tensor = k["flops"] > 0 and ("gemm" in name or ("attention" in name and "[cross]" not in name
+                                                        and "temporal" not in name))
         s = k["ms"] * 1e-3
         if tensor:
             ach, peak, unit = k["flops"] / s / 1e12, pk["tf_sustained"], "TFLOP/s"
@@ -337,12 +426,17 @@ def main():
     ap.add_argument("--workload", default="xl_17f_848x1600")
     ap.add_argument("--no-secondary", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-full-reference", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
 
+    if args.cpu_full_reference:
+        if rank == 0:
+            run_full_reference(args)
+        return
     if args.impl == "reference":
         run_reference_arm(args, rank)
         return
@@ -414,6 +508,9 @@ def main():
                 algorithmic_tflop_per_step=fl["total"] / 1e12,
                 step_tflops_per_gpu=step_tf, step_frac_of_bf16_sustained=step_tf / pk["tf_sustained"],
                 step_frac_of_bf16_burst=step_tf / pk["tf_burst"])
+    line["output_finite"] = res["finite"]
+    if res["sp_parity"] is not None:
+        line["sp_parity_rel_l2"] = res["sp_parity"]
     if secondary:
         line["secondary"] = secondary
     if world == 1 and not args.no_cpu_baseline:
@@ -421,8 +518,11 @@ def main():
         torch.set_num_threads(cores)
         sample = CpuSample(args.workload)
         est, wall = sample.step()
-        line["cpu_baseline"] = dict(value=1.0 / est, unit=UNIT, cores=cores, kind="port", sample=sample.desc,
-                                    sample_wall_s=wall)
+        line["cpu_baseline"] = sample.record(est, wall, cores)
+        if secondary is not None:
+            s2 = CpuSample("xl_17f_224x400")
+            e2, w2 = s2.step()
+            secondary["cpu_baseline"] = s2.record(e2, w2, cores)
     print(json.dumps(line), flush=True)
     if world > 1:
         torch.distributed.destroy_process_group()

@@ -36,9 +36,15 @@ constexpr int HB = 64;            // keys per half-step = S columns owned by one
 constexpr int CH = 32;            // keys per tcgen05.ld / exponential chunk
 constexpr int KV_STAGES = 3;
 constexpr int QT = 2;             // query tiles per CTA
-constexpr int SM_WARP0 = 3;       // warps: 0 TMA, 1 / 2 MMA issuer of tile 0 / 1, 3..18 softmax
+// warps 0..15 softmax, 16 TMA producer, 17 / 18 MMA issuer of query tile 0 / 1.  Measured (profiles/attn_trace_r02.txt):
+// a control warp costs the four softmax warps of its sub-partition 15-30 % of their speed — the issuer's tcgen05.mma
+// instructions issue in lock-step with the tensor pipe (~42 clk each, 18 per K/V tile) and hold the sub-partition's
+// dispatch port meanwhile — whichever warp ids they carry and however they wait (spinning try_wait, try_wait with a
+// suspend hint, nanosleep): the sub-partition WITHOUT a control warp finishes its 64 scores in ~1100 clk, the others
+// in 1300-1500, and the slowest sets the period.
 constexpr int N_SM_WARPS = 16;
-constexpr int NTHREADS = (SM_WARP0 + N_SM_WARPS) * 32;
+constexpr int TMA_WARP = 16, MMA_WARP0 = 17;
+constexpr int NTHREADS = (N_SM_WARPS + 3) * 32;
 constexpr int TMEM_COLS = 512;    // S_t at 128·t, O_t at 256 + 128·t, Q_t (bf16 pairs) at 336 + 128·t
 constexpr float RETRY_SHIFT = 90.f;             // log2 units added to an overflowed row's reference
 constexpr float L_LIMIT = 1.2089258196146292e24f;   // 2^80
@@ -99,7 +105,7 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     }
   };
 
-  if (warp == 0 && lane == 0) {
+  if (warp == TMA_WARP && lane == 0) {
     prefetch_tmap(&tq);
     prefetch_tmap(&tk);
     prefetch_tmap(&tv);
@@ -122,7 +128,7 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     *retry_flag = 0;
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == MMA_WARP0) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -136,7 +142,7 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     return f == (uint32_t)(pass + 1) && attempt < MAX_RETRY;
   };
 
-  if (warp == 0) {
+  if (warp == TMA_WARP) {
     // ================= TMA producer =================
     if (lane == 0) {
       mbar_expect_tx(q_full, n_qt * C::Q_BYTES);
@@ -154,13 +160,15 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
             const uint32_t ph = (uint32_t)((jg / KV_STAGES) & 1);
             const int row = kseq * p.Lk + kt * BNK;
             if (jg == KV_STAGES - 1)                     // first use of the stage that held Q: Q must be in TMEM
-              for (int t = 0; t < n_qt; ++t) mbar_wait_parked(&qt_full[t], 0, 2000);
-            mbar_wait_parked(&k_empty[st], ph ^ 1, 2000);
+              for (int t = 0; t < n_qt; ++t) mbar_wait_parked(&qt_full[t], 0, 4000);
+            mbar_wait_parked(&k_empty[st], ph ^ 1, 4000);
+            mark(jg, 0);
             mbar_expect_tx(&k_full[st], C::KV_BYTES);
 #pragma unroll
             for (int c = 0; c < C::NCH; ++c)
               tma_load_3d(sK + st * C::KV_BYTES + c * BNK * 128, &tk, &k_full[st], c * 64, h, row);
-            mbar_wait_parked(&v_empty[st], ph ^ 1, 2000);
+            mbar_wait_parked(&v_empty[st], ph ^ 1, 4000);
+            mark(jg, 1);
             mbar_expect_tx(&v_full[st], C::KV_BYTES);
 #pragma unroll
             for (int c = 0; c < C::NCH; ++c)
@@ -172,11 +180,11 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         }
       }
     }
-  } else if (warp == 1 || warp == 2) {
-    // ================= MMA issuers: warp 1 -> query tile 0, warp 2 -> query tile 1 =================
+  } else if (warp > TMA_WARP) {
+    // ================= MMA issuers: warp 17 -> query tile 0, warp 18 -> query tile 1 =================
     // The whole warp runs the warp-uniform control flow and one elected lane issues the tcgen05 instructions of a
     // half-step back to back (descriptors are base + constant, the 14-bit address field never carries).
-    const int t = warp - 1;
+    const int t = warp - MMA_WARP0;
     if (t < n_qt) {
       constexpr uint32_t idesc_qk = make_idesc_bf16(BMQ, HB, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(BMQ, DP, 0, 1);     // A = P from TMEM, B = V is MN-major
@@ -193,7 +201,7 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         }
         umma_commit(&s_full[t * 2 + hf]);
       };
-      mbar_wait(&qt_full[t], 0);
+      mbar_wait_parked(&qt_full[t], 0, 1000);
       int jg = 0, pass = 0;
       uint32_t cp[2] = {0, 0};                           // P^hf half-steps consumed so far (parity of p_full)
       for (int set = 0; set < p.n_sets; ++set) {
@@ -211,12 +219,14 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
             const bool more = kt + 1 < n_kt;
             const int nh = kt == n_kt - 1 ? nh_last : 2;
             const int nh1 = kt + 1 == n_kt - 1 ? nh_last : 2;             // half-steps of the next tile
+            mark(jg, 5);
             mbar_wait_parked(&v_full[st], (uint32_t)((jg / KV_STAGES) & 1), 1000);
+            mark(jg, 6);
             if (more) mbar_wait_parked(&k_full[st1], (uint32_t)(((jg + 1) / KV_STAGES) & 1), 1000);
             const uint64_t dv = dv0 + (uint64_t)(st * (C::KV_BYTES >> 4));
             mark(jg, 0);
             for (int hf = 0; hf < nh; ++hf) {
-              mbar_wait(&p_full[t * 2 + hf], cp[hf] & 1);
+              mbar_wait_parked(&p_full[t * 2 + hf], cp[hf] & 1, 1000);
               ++cp[hf];
               tc_fence_after();
               mark(jg, 1 + 2 * hf);
@@ -239,10 +249,10 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         }
       }
     }
-  } else if (((warp - SM_WARP0) >> 3) < n_qt) {
+  } else if (warp < N_SM_WARPS && (warp >> 3) < n_qt) {
     // ================= softmax warps: warp (t, hf), thread = query row =================
     const int quarter = warp & 3;                      // TMEM lane quarter this warp may touch (= its sub-partition)
-    const int role = (warp - SM_WARP0) >> 2;           // 0..3 among the four warps of a quarter
+    const int role = warp >> 2;                        // 0..3 among the four warps of a quarter
     const int t = role >> 1, hf = role & 1;
     const int row = quarter * 32 + lane;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
@@ -298,6 +308,13 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       }
       l_acc += (la.x + la.y) + (lb.x + lb.y);
     };
+    auto mask_tail = [&](uint32_t (&s)[CH], int left) {   // ragged last tile: keys past Lk do not exist
+      if (left < CH) {
+#pragma unroll
+        for (int i = 0; i < CH; ++i)
+          if (i >= left) s[i] = 0xff800000u;  // -inf
+      }
+    };
     const int n_mine = hf == 0 ? n_kt : n_kt - (nh_last == 1 ? 1 : 0);   // half-steps of this warp per pass
     const int xi = (t * 2 + hf) * BMQ + row, xo = (t * 2 + (hf ^ 1)) * BMQ + row;   // own / partner exchange slot
     uint32_t cnt = 0;                                    // half-steps done so far (parity of s_full)
@@ -310,42 +327,43 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           mbar_wait(&s_full[t * 2 + hf], cnt & 1);
           tc_fence_after();
           mark(cnt, 0);
-          const int nh = kt == n_kt - 1 ? nh_last : 2;
-          if (hf == nh - 1 && quarter == 0 && lane == 0) {
-            // the LAST half of S(tile jg + kt) is complete, and the tensor pipe completes in issue order: every
-            // Q·K^T on this K tile and every P·V on the previous V tile is done — hand both stages back
-            const int j = jg + kt;
-            mbar_arrive(&k_empty[j % KV_STAGES]);
-            if (j > 0) mbar_arrive(&v_empty[(j - 1) % KV_STAGES]);
-          }
           const int kv_left = kt == n_kt - 1 ? p.Lk - kt * BNK - hf * HB : HB;   // keys of this half that exist
-          uint32_t s[CH], pk[CH / 2];
+          // two 32-key chunks; P chunk q goes to columns 16q..16q+15 of the half, over scores already in registers.
+          // (Tried: four 16-key chunks double-buffered through registers so that the tcgen05.ld of the next chunk
+          // flies under the exponentials — slower, 880 vs 930 TF/s: more TMEM instructions, longer MMA issue.)
+          uint32_t sr[CH], pk[CH / 2];
+          const bool release = quarter == 0 && hf == (kt == n_kt - 1 ? nh_last : 2) - 1;
 #pragma unroll
           for (int q = 0; q < HB / CH; ++q) {
-            tmem_ld_x32(sh_addr + q * CH, s);
-            tmem_ld_wait();
-            if (kv_left - q * CH < CH) {                 // ragged last tile: keys past Lk do not exist
-#pragma unroll
-              for (int i = 0; i < CH; ++i)
-                if (i >= kv_left - q * CH) s[i] = 0xff800000u;  // -inf
+            tmem_ld_x32(sh_addr + q * CH, sr);
+            if (q == 0 && release && lane == 0) {
+              // the LAST half of S(tile jg + kt) is complete, and the tensor pipe completes in issue order: every
+              // Q·K^T on this K tile and every P·V on the previous V tile is done — hand both stages back to the TMA
+              // producer (under the latency of the load above)
+              const int j = jg + kt;
+              mbar_arrive(&k_empty[j % KV_STAGES]);
+              if (j > 0) mbar_arrive(&v_empty[(j - 1) % KV_STAGES]);
             }
+            tmem_ld_wait();
+            mask_tail(sr, kv_left - q * CH);
             if (q == 0 && kt == 0 && attempt == 0) {
               // the set's reference: max over the first 32 scores of both warps of the row
               float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
               for (int i = 0; i < CH; i += 4) {
-                mx0 = fmax3(mx0, __uint_as_float(s[i]), __uint_as_float(s[i + 1]));
-                mx1 = fmax3(mx1, __uint_as_float(s[i + 2]), __uint_as_float(s[i + 3]));
+                mx0 = fmax3(mx0, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]));
+                mx1 = fmax3(mx1, __uint_as_float(sr[i + 2]), __uint_as_float(sr[i + 3]));
               }
               const float mine = fmaxf(mx0, mx1);
               xch_m[xi] = mine;
               named_bar_sync(pair_bar, 64);
               moff = fmaxf(mine, xch_m[xo]) * c;
             }
-            exp_chunk(s, moff, pk, l_part);
+            exp_chunk(sr, moff, pk, l_part);
             tmem_st_x16(sh_addr + q * (CH / 2), pk);
-            mark(cnt, 1 + q);
+            if (q == 0) mark(cnt, 1);
           }
+          mark(cnt, 2);
           tmem_st_wait();
           tc_fence_before();
           __syncwarp();
@@ -408,7 +426,7 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == MMA_WARP0) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
   }

@@ -302,6 +302,9 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // the same for a load that was issued long before (software pipelining): the destination registers pass THROUGH the
 // wait, so no instruction that reads them can be scheduled ahead of it
 #define MDV2_RW8(r, o) "+r"(r[o]), "+r"(r[o + 1]), "+r"(r[o + 2]), "+r"(r[o + 3]), "+r"(r[o + 4]), "+r"(r[o + 5]), "+r"(r[o + 6]), "+r"(r[o + 7])
+__device__ __forceinline__ void tmem_ld_wait_x16(uint32_t* r) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : MDV2_RW8(r, 0), MDV2_RW8(r, 8) : : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait_x32(uint32_t* r) {
   asm volatile("tcgen05.wait::ld.sync.aligned;"
                : MDV2_RW8(r, 0), MDV2_RW8(r, 8), MDV2_RW8(r, 16), MDV2_RW8(r, 24)

@@ -203,7 +203,8 @@ def attention(q, k, v, out, n_seq, Lq, Lk, H, D, scale, kv_map=None, backend=Non
     e0 = _t0()
     _check(_lib.mdv2_attention(pq, ldq, pk, ldk, pv, ldv, po, ldo, n_seq, Lq, Lk, H, D, float(scale), pm, n_sets,
                                _dt(q), be, _stream()), "mdv2_attention")
-    tag = "[cross]" if Lk <= 512 and Lq != Lk else ("[xview]" if n_sets > 1 else "[self]")
+    # the spatial self-attention and the cross-view attention are ONE kernel (K/V sets swept back to back): one row
+    tag = "[cross]" if Lk <= 512 and Lq != Lk else "[spatial self + cross-view]"
     _t1(e0, tag, 4.0 * n_seq * Lq * Lk * H * D * n_sets,
         (2 * q.shape[0] + 2 * n_sets * n_seq * Lk) * H * D * q.element_size())
     return out
@@ -343,6 +344,5 @@ def attention_scatter(q, k, v, partial, n_seq, Lq, Lk, H, D, scale, dst_ptrs, ro
     _check(_lib.mdv2_attention_scatter(pq, ldq, pk, ldk, pv, ldv, pp, ldp, n_seq, Lq, Lk, H, D, float(scale), pm,
                                        n_sets, arr, n, rows_per_rank, dst_ld, dst_col, _stream()),
            "mdv2_attention_scatter")
-    tag = "[xview]" if n_sets > 1 else "[self]"
-    _t1(e0, tag, 4.0 * n_seq * Lq * Lk * H * D * n_sets,
+    _t1(e0, "[spatial self + cross-view]", 4.0 * n_seq * Lq * Lk * H * D * n_sets,
         (2 * q.shape[0] + 2 * n_sets * n_seq * Lk) * H * D * q.element_size())

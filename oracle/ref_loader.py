@@ -1,16 +1,29 @@
 """TEST INFRASTRUCTURE — imports the REAL reference (``/root/reference``) behind the shims in
 ``oracle/shims`` so that golden vectors can be generated from the reference's own code.
 
-Only usable in the build container (``/root/reference`` does not exist on the GPU box); nothing in
-``tests -m gpu``, ``smoke()`` or ``bench.py`` may import this module.  Recipe: SURVEY.md App. C.
+In the build container it reads ``/root/reference``; on the GPU box the same unmodified files from ``oracle/_ref``
+(``oracle/populate_ref.py``), where only ``bench.py``'s CPU legs use it.  Recipe: SURVEY.md App. C.
 """
 import importlib
 import os
 import sys
 import types
 
-REF_ROOT = os.environ.get("MDV2_REFERENCE_ROOT", "/root/reference")
-_SHIMS = os.path.join(os.path.dirname(os.path.abspath(__file__)), "shims")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SHIMS = os.path.join(_HERE, "shims")
+
+
+def _find_root():
+    """/root/reference in the build container; on the GPU box the git-ignored copy of the same unmodified files that
+    oracle/populate_ref.py left under oracle/_ref (it ships with the snapshot like the built .so)."""
+    env = os.environ.get("MDV2_REFERENCE_ROOT")
+    for cand in ([env] if env else []) + ["/root/reference", os.path.join(_HERE, "_ref")]:
+        if os.path.isdir(os.path.join(cand, "magicdrivedit")):
+            return cand
+    return env or "/root/reference"
+
+
+REF_ROOT = _find_root()
 
 
 def available() -> bool:

@@ -10,7 +10,9 @@ from magicdrive_v2_b200 import synth
 
 pytestmark = pytest.mark.gpu
 CASES = [("tiny_1f", "ones"), ("tiny_1f_image", "ones"), ("tiny_9f", "ones"), ("tiny_9f", "first0"), ("tiny_9f", None),
-         ("tiny_d72", "first0")]
+         ("tiny_d72", "first0"),
+         ("tiny_65f", "first0"),     # 65 pixel frames -> T = 17: the long-clip temporal kernel at model level
+         ("tiny_l62", "ones")]       # 20 boxes + 40 text tokens -> 62 condition tokens, D = 72 heads
 
 
 def _run(wl_name, xm, dtype):
@@ -36,7 +38,11 @@ def test_fp32_matches_reference(wl_name, xm):
 def test_bf16_matches_reference(wl_name, xm):
     err, fix = _run(wl_name, xm, torch.bfloat16)
     print(f"bf16 {wl_name}/{xm}: rel L2 {err:.3e} (reference's own bf16 gap {fix['ref_bf16_rel_l2']:.3e})")
-    assert err < 1e-2
+    # north star: <= 1e-2.  Where the REFERENCE's own bf16 forward is already further than that from its fp32 forward
+    # (tiny_l62: 1.06e-2 — the bound is of the order of bf16 noise), no bf16 implementation can be asked for more than
+    # "no further from the fp32 reference than the reference's own bf16 run": that is then the bound, not a wider one.
+    ref_gap = fix["ref_bf16_rel_l2"]
+    assert err < (1e-2 if ref_gap <= 1e-2 else ref_gap)
 
 
 def test_native_library_is_the_path_that_runs():
@@ -90,11 +96,10 @@ def test_sde_brushnet_matches_reference(fixture, skip_ca, dtype, tol):
 
 
 @pytest.mark.parametrize("name", ["ctrl_xview", "drop_masks"])
-@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1.2e-2)])
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2)])
 def test_variants_match_reference(name, dtype, tol):
     """Control blocks with cross-view attention; dropped conditions / frames — through libmdv2 against the REAL
-    reference.  (bf16 bound 1.2e-2: these fixtures do not store the reference's own bf16 gap, which is 1.0-1.05e-2
-    on the sibling cases.)"""
+    reference, at the north-star tolerances."""
     from helpers import variant_case
     wl_name, kw, inp = variant_case(name)
     fix = load_golden(f"variant_{name}.pt")
@@ -105,3 +110,32 @@ def test_variants_match_reference(name, dtype, tol):
     err = rel_l2(out.cpu(), fix["out"])
     print(f"variant {name} {dtype}: rel L2 {err:.3e}")
     assert torch.isfinite(out).all() and err < tol
+
+
+def _xl_case(dtype):
+    fix = load_golden("xl_17f_224x400_b1_first0.pt")
+    model, wl, kw = build_model("xl_17f_224x400_b1")          # 28 + 13 blocks, hidden 1152; CPU-seeded weights
+    model = model.to("cuda", dtype)
+    inp = synth.to_device(synth.make_inputs(wl, seed=fix["seed"], x_mask="first0", kw=kw), "cuda")
+    out = model(**inp)
+    torch.cuda.synchronize()
+    assert out.dtype == torch.float32 and out.shape == fix["out"].shape and torch.isfinite(out).all()
+    return rel_l2(out.cpu(), fix["out"]), fix
+
+
+def test_xl_depth_fp32_matches_reference():
+    """MagicDriveSTDiT3-XL/2 at full depth (configs[1] at b = 1: 6 views x 17 frames x 224x400) against ONE fp32 CPU
+    forward of the REAL reference (oracle/make_golden_xl.py; magicdrive_stdit3.py:1021-1218)."""
+    err, _ = _xl_case(torch.float32)
+    print(f"XL fp32: rel L2 {err:.3e}")
+    assert err < 1e-4
+
+
+def test_xl_depth_bf16_vs_reference():
+    """The same in bf16.  At depth 28 the REFERENCE's own bf16 forward is 2.36e-2 away from its fp32 forward (stored
+    in the fixture), so 1e-2 is not a bound any bf16 implementation of this depth meets; what is asserted is that the
+    bf16 drop-in is no further from the fp32 reference than the reference's own bf16 run, and the 1e-2 figure of the
+    north star is reported beside it (and asserted on every depth-2 configuration above)."""
+    err, fix = _xl_case(torch.bfloat16)
+    print(f"XL bf16: rel L2 {err:.3e} vs fp32 reference; the reference's own bf16 forward: {fix['ref_bf16_rel_l2']:.3e}")
+    assert err <= fix["ref_bf16_rel_l2"]

@@ -233,29 +233,35 @@ def _attn_case(n_seq, Lq, Lk, H, D, *, kv="self", seed=0, q_gain=1.0):
     return rel_l2(out, ref)
 
 
+# measured: 2.1e-3 .. 2.4e-3 on every shape (tools/bench_attn.py accuracy(), profiles/yardstick_attn_r02.txt) — the bf16
+# rounding of P and of the output; the bound is ~2x that, so a mis-scaled tail tile or a lost K/V tile fails
+ATTN_TOL = 5e-3
+
+
 @pytest.mark.parametrize("D", [64, 72])
 @pytest.mark.parametrize("L", [128, 256, 400, 77])
 def test_attention_tcgen05_self(D, L):
-    assert _attn_case(6, L, L, 4, D) < 2e-2
+    assert _attn_case(6, L, L, 4, D) < ATTN_TOL
 
 
 @pytest.mark.parametrize("D", [64, 72])
 def test_attention_tcgen05_cross_view_and_cross(D):
-    assert _attn_case(6, 400, 400, 4, D, kv="xview") < 2e-2
-    assert _attn_case(6, 400, 62, 4, D, kv="cross") < 2e-2          # one ragged K/V tile
-    assert _attn_case(6, 350, 150, 4, D, kv="cross") < 2e-2         # two K/V tiles, ragged
+    assert _attn_case(6, 400, 400, 4, D, kv="xview") < ATTN_TOL
+    assert _attn_case(6, 400, 62, 4, D, kv="cross") < ATTN_TOL          # one ragged K/V tile
+    assert _attn_case(6, 350, 150, 4, D, kv="cross") < ATTN_TOL         # two K/V tiles, ragged
 
 
 def test_attention_tcgen05_xl_shape():
-    assert _attn_case(12, 1400, 1400, 16, 72) < 2e-2
+    assert _attn_case(12, 1400, 1400, 16, 72) < ATTN_TOL
+    assert _attn_case(3, 1600, 1600, 16, 72) < ATTN_TOL            # 12.5 key tiles: the last tile's second half is skipped
 
 
 @pytest.mark.parametrize("gain", [6.0, 20.0])
 def test_attention_tcgen05_rescale_path(gain):
     """Scores with a spread of tens of log2 units: the running maximum keeps outgrowing the lazy-rescale
     threshold, so the in-TMEM rescale of O and the repeated exponential pass are exercised on most tiles."""
-    assert _attn_case(4, 1000, 1000, 4, 72, q_gain=gain) < 2e-2
-    assert _attn_case(4, 600, 600, 4, 72, kv="xview", q_gain=gain) < 2e-2
+    assert _attn_case(4, 1000, 1000, 4, 72, q_gain=gain) < ATTN_TOL
+    assert _attn_case(4, 600, 600, 4, 72, kv="xview", q_gain=gain) < ATTN_TOL
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])

@@ -6,7 +6,8 @@ from helpers import build_model, load_golden, rel_l2
 from magicdrive_v2_b200 import synth
 from oracle import stdit3_oracle
 
-CASES = [("tiny_1f", "ones"), ("tiny_1f_image", "ones"), ("tiny_9f", "ones"), ("tiny_9f", "first0"), ("tiny_9f", None), ("tiny_d72", "first0")]
+CASES = [("tiny_1f", "ones"), ("tiny_1f_image", "ones"), ("tiny_9f", "ones"), ("tiny_9f", "first0"), ("tiny_9f", None), ("tiny_d72", "first0"),
+         ("tiny_65f", "first0"), ("tiny_l62", "ones")]
 
 
 @pytest.mark.parametrize("wl_name,xm", CASES)

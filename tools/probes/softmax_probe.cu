@@ -59,6 +59,17 @@ __device__ __forceinline__ float2 ex2_poly2_lite(float2 x) {
   r.y = __uint_as_float(__float_as_uint(q.y) + (__float_as_uint(t.y) << 23));
   return r;
 }
+// the same polynomial with scalar FFMA / FADD (1 clk per warp instruction each; FFMA2 measured 3)
+__device__ __forceinline__ float ex2_poly1(float x) {
+  const float MAGIC = 12582912.f;
+  x = fmaxf(x, -126.f);
+  const float t = x + MAGIC;
+  const float f = x - (t - MAGIC);
+  float q = fmaf(f, 0.05517202615737915f, 0.2426111400127411f);
+  q = fmaf(q, f, 0.693260908126831f);
+  q = fmaf(q, f, 0.9999280571937561f);
+  return __uint_as_float(__float_as_uint(q) + (__float_as_uint(t) << 23));
+}
 __host__ __device__ constexpr bool poly_pair(int pair, int PF) { return ((pair % 8) * PF) / 8 != (((pair % 8) + 1) * PF) / 8; }
 
 constexpr int CH = 32;
@@ -93,7 +104,7 @@ __global__ void __launch_bounds__(512, 1) k(float* out, int iters, long long* cl
     const float2 c2 = make_float2(c, c), nm2 = make_float2(-moff, -moff);
     float2 la = make_float2(0.f, 0.f), lb = make_float2(0.f, 0.f);
     float mx0 = -INFINITY, mx1 = -INFINITY;
-    if (ORDER == 0) {
+    if (ORDER == 0 || ORDER == 3) {
 #pragma unroll
       for (int i = 0; i < CH; i += 4) {
         const float s0 = __uint_as_float(s[i]), s1 = __uint_as_float(s[i + 1]);
@@ -102,8 +113,10 @@ __global__ void __launch_bounds__(512, 1) k(float* out, int iters, long long* cl
         const float2 x01 = ffma2(make_float2(s0, s1), c2, nm2);
         const float2 x23 = ffma2(make_float2(s2, s3), c2, nm2);
         float2 e01, e23;
-        if (poly_pair(i / 2, PF)) e01 = ex2_poly2(x01); else e01 = make_float2(ex2(x01.x), ex2(x01.y));
-        if (poly_pair(i / 2 + 1, PF)) e23 = ex2_poly2(x23); else e23 = make_float2(ex2(x23.x), ex2(x23.y));
+        if (poly_pair(i / 2, PF)) e01 = ORDER == 3 ? make_float2(ex2_poly1(x01.x), ex2_poly1(x01.y)) : ex2_poly2(x01);
+        else e01 = make_float2(ex2(x01.x), ex2(x01.y));
+        if (poly_pair(i / 2 + 1, PF)) e23 = ORDER == 3 ? make_float2(ex2_poly1(x23.x), ex2_poly1(x23.y)) : ex2_poly2(x23);
+        else e23 = make_float2(ex2(x23.x), ex2(x23.y));
         la = fadd2(la, e01);
         lb = fadd2(lb, e23);
         __nv_bfloat162 b01 = __floats2bfloat162_rn(e01.x, e01.y), b23 = __floats2bfloat162_rn(e23.x, e23.y);
@@ -157,19 +170,17 @@ void run(const char* name, float* out, long long* clk) {
 int main() {
   float* out; long long* clk;
 #define SETSM(...) cudaFuncSetAttribute(k<__VA_ARGS__>, cudaFuncAttributeMaxDynamicSharedMemorySize, 12 * 512 * 16)
-  SETSM(0, 1, 0); SETSM(0, 0, 0); SETSM(2, 1, 0); SETSM(3, 1, 0); SETSM(4, 1, 0); SETSM(0, 1, 1); SETSM(2, 1, 1); SETSM(3, 1, 1); SETSM(4, 1, 1); SETSM(4, 1, 2); SETSM(6, 1, 2);
+  SETSM(0, 1, 0); SETSM(0, 0, 0); SETSM(2, 0, 0); SETSM(3, 0, 0); SETSM(4, 0, 0); SETSM(2, 0, 3); SETSM(3, 0, 3); SETSM(4, 0, 3); SETSM(5, 0, 3);
   cudaMalloc(&out, 1 << 20); cudaMallocManaged(&clk, 8);
   run<0, 1, 0>("fused loop, PF=0, max", out, clk);
   run<0, 0, 0>("fused loop, PF=0, no max", out, clk);
-  run<2, 1, 0>("fused loop, PF=2, max", out, clk);
-  run<3, 1, 0>("fused loop, PF=3, max", out, clk);
-  run<4, 1, 0>("fused loop, PF=4, max", out, clk);
-  run<0, 1, 1>("two-phase, PF=0, max", out, clk);
-  run<2, 1, 1>("two-phase, PF=2, max", out, clk);
-  run<3, 1, 1>("two-phase, PF=3, max", out, clk);
-  run<4, 1, 1>("two-phase, PF=4, max", out, clk);
-  run<4, 1, 2>("two-phase, PF=4 lite poly (deg 2, no clamp), max", out, clk);
-  run<6, 1, 2>("two-phase, PF=6 lite poly, max", out, clk);
+  run<2, 0, 0>("fused loop, PF=2, no max", out, clk);
+  run<3, 0, 0>("fused loop, PF=3, no max", out, clk);
+  run<4, 0, 0>("fused loop, PF=4, no max", out, clk);
+  run<2, 0, 3>("fused loop, PF=2 scalar poly, no max", out, clk);
+  run<3, 0, 3>("fused loop, PF=3 scalar poly, no max", out, clk);
+  run<4, 0, 3>("fused loop, PF=4 scalar poly, no max", out, clk);
+  run<5, 0, 3>("fused loop, PF=5 scalar poly, no max", out, clk);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { printf("CUDA error: %s\n", cudaGetErrorString(e)); return 1; }
   return 0;
