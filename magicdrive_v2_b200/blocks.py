@@ -113,6 +113,10 @@ class STDiT3Block(nn.Module):
             else:
                 ops.gemm(ws.xm[rows], W(a.qkv), a.qkv.bias, ws.qkv[rows], geo=geo, rms=(qn, kn, D, C, C))
 
+        # the fused projection + NVLink scatter needs the q / k RMSNorm epilogue (mdv2_gemm_qkv_scatter): with
+        # qk_norm=False the sequence-parallel path keeps the plain GEMM and the separate scatter kernel
+        qkv_rows.fusable = qn is not None and kn is not None
+
         def proj_rows(rows, tab):
             ops.gemm(ws.ao[rows], W(a.proj), a.proj.bias, x[rows], geo=geo, gate=(tab(mod), 2), res=x[rows])
 

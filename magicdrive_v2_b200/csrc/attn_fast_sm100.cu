@@ -436,7 +436,7 @@ template <int DP, int PF, bool TRACE>
 int launch_fast(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p, int n_seq,
                 cudaStream_t st) {
   constexpr int SMEM = FCfg<DP>::SMEM;
-  static bool configured = false;
+  static PerDeviceFlag configured_flag; bool& configured = configured_flag.here();
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(attn_fast_kernel<DP, PF, TRACE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     if (e != cudaSuccess) {

@@ -473,7 +473,7 @@ int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap&
                 cudaStream_t st) {
   using C = ACfg<DP, BNK>;
   constexpr int SMEM = C::SMEM;
-  static bool configured = false;
+  static PerDeviceFlag configured_flag; bool& configured = configured_flag.here();
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(attn_sm100_kernel<DP, BNK, PF, TRACE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     if (e != cudaSuccess) {

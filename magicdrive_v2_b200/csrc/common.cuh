@@ -107,6 +107,17 @@ static inline int mdv2_num_sms() {
   return n;
 }
 
+// cudaFuncSetAttribute (dynamic shared memory opt-in) is per DEVICE: one flag per (call site, device), so a process that
+// drives several GPUs configures each kernel on each of them
+struct PerDeviceFlag {
+  bool done[64] = {};
+  bool& here() {
+    int d = 0;
+    cudaGetDevice(&d);
+    return done[d & 63];
+  }
+};
+
 // output scatter of the tcgen05 attention kernel under sequence parallelism (see AParams in attn_sm100.cu)
 struct AttnScatter {
   void* const* dst;

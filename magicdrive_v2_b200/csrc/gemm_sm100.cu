@@ -419,7 +419,7 @@ namespace {
 template <int BN, int HD>
 int launch(const CUtensorMap& ta, const CUtensorMap& tw, const Params& p, cudaStream_t st) {
   using C = Cfg<BN, HD>;
-  static bool configured = false;
+  static PerDeviceFlag configured_flag; bool& configured = configured_flag.here();
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(gemm_sm100_kernel<BN, HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
     if (e != cudaSuccess) {

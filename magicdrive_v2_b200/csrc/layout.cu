@@ -831,7 +831,7 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
       static const int short_mma = getenv("MDV2_TEMPORAL_MMA") != nullptr;       // A/B hook: tensor-core phases B + C
 #define TS_CASE(TT)                                                                                               \
   case TT: {                                                                                                      \
-    static bool configured = false;                                                                               \
+    static PerDeviceFlag configured_flag; bool& configured = configured_flag.here();                                                                               \
     if (!configured) {                                                                                            \
       cudaFuncSetAttribute(temporal_attn_smem_kernel<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024); \
       configured = true;                                                                                          \
@@ -846,11 +846,14 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
       MDV2_CHECK_LAUNCH("temporal_attention");
       return MDV2_OK;
     }
-    if (!legacy && Tn > 8 && Tn <= 32 && D % 8 == 0 && ld % 8 == 0 && ldo % 8 == 0 && ((uintptr_t)qkv % 16 == 0) &&
+    if (!legacy && Tn > 8 && Tn <= 128 && D % 8 == 0 && ld % 8 == 0 && ldo % 8 == 0 && ((uintptr_t)qkv % 16 == 0) &&
         ((uintptr_t)out % 16 == 0) && ((uintptr_t)c % 16 == 0) && ((uintptr_t)s % 16 == 0)) {
       // largest head group (a divisor of H, at most 8 heads) whose staged frames + score table leave room for three
       // CTAs per SM
-      static const bool scalar = getenv("MDV2_TEMPORAL_LONG_SCALAR") != nullptr;     // A/B hook
+      // (the warp-level MMA phases hold a 32 x 32 score tile per head; longer clips — 129 frames -> T = 33, the
+      // reference's "full" 241-frame config -> T = 61 — take the scalar phases, which loop over T)
+      static const bool scalar_env = getenv("MDV2_TEMPORAL_LONG_SCALAR") != nullptr;     // A/B hook
+      const bool scalar = scalar_env || Tn > 32;
       const int Tp = (Tn + 3) & ~3;
       auto smem_long = [&](int g) {
         return (size_t)Tn * (3 * g * D * 2 + TA_PAD) + 16 + (scalar ? (size_t)g * Tn * Tp * 4 : 0);
@@ -863,7 +866,7 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
         }
       const int64_t n_ctas = (int64_t)B * S * (HG ? H / HG : 0);
       if (HG && n_ctas <= 0x7fffffff) {
-        static bool configured = false;
+        static PerDeviceFlag configured_flag; bool& configured = configured_flag.here();
         if (!configured) {
           cudaFuncSetAttribute(temporal_attn_smem_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024);
           configured = true;
@@ -896,9 +899,9 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
   temporal_attn_kernel<T, TM, PP><<<grid, block, 0, st>>>((const T*)qkv, ld, c, s, (T*)out, ldo, n_warps, \
                                                           Tn, S, H, D, scale)
   if (ppl == 1) {
-    if (Tn <= 8) TA_CASE(8, 1); else TA_CASE(32, 1);
+    if (Tn <= 8) TA_CASE(8, 1); else if (Tn <= 32) TA_CASE(32, 1); else TA_CASE(64, 1);
   } else {
-    if (Tn <= 8) TA_CASE(8, 2); else TA_CASE(32, 2);
+    if (Tn <= 8) TA_CASE(8, 2); else if (Tn <= 32) TA_CASE(32, 2); else TA_CASE(64, 2);
   }
 #undef TA_CASE
   MDV2_CHECK_LAUNCH("temporal_attention");
@@ -909,7 +912,10 @@ extern "C" int mdv2_temporal_attention(const void* qkv, int64_t ld, const float*
                                        void* out, int64_t ldo, int B, int T, int S, int H, int D, float scale,
                                        int dtype, void* stream) {
   if ((int64_t)B * S * H == 0) return MDV2_OK;
-  MDV2_REQUIRE(T >= 1 && T <= 32, "temporal_attention: T=%d unsupported (1..32)", T);
+  // bf16: T <= 8 staged kernel, 8 < T <= 32 warp-MMA kernel, 32 < T <= 128 the same staging with scalar phases;
+  // fp32 (validation mode) and the shapes the staged kernels do not take: the register kernel, T <= 64
+  MDV2_REQUIRE(T >= 1 && T <= (dtype == 1 ? 128 : 64), "temporal_attention: T=%d unsupported (1..%d)", T,
+               dtype == 1 ? 128 : 64);
   MDV2_REQUIRE(D % 2 == 0 && D <= 128, "temporal_attention: head_dim=%d unsupported", D);
   MDV2_REQUIRE(ld % 2 == 0 && ldo % 2 == 0, "temporal_attention: odd leading dimension");
   cudaStream_t st = (cudaStream_t)stream;

@@ -24,10 +24,25 @@ class Registry:
             return obj
         return _reg(module) if module is not None else _reg
 
+    @staticmethod
+    def _populate():
+        """The reference's ``models/__init__`` fills the registry on import; here the model / sampler modules register
+        themselves when imported, so every lookup imports them first (they load the CUDA library lazily: safe
+        without libmdv2.so)."""
+        from . import brushnet, rflow, stdit3  # noqa: F401
+
     def get(self, key):
+        self._populate()
         return self._modules.get(key)
 
+    def __getitem__(self, key):
+        self._populate()
+        if key not in self._modules:
+            raise KeyError(f"{key} is not in the {self.name} registry")
+        return self._modules[key]
+
     def __contains__(self, key):
+        self._populate()
         return key in self._modules
 
     def build(self, cfg: dict, **kwargs):
@@ -36,6 +51,7 @@ class Registry:
         if "type" not in cfg:
             raise KeyError(f"`cfg` must contain the key \"type\", but got {cfg}")
         key = cfg.pop("type")
+        self._populate()
         if key not in self._modules:
             raise KeyError(f"{key} is not in the {self.name} registry")
         return self._modules[key](**cfg)

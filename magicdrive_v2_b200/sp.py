@@ -10,8 +10,12 @@ tokens) are replicated — the reference's 164 all-to-alls there are dropped.
 """
 from __future__ import annotations
 
+import logging
+
 import torch
 import torch.distributed as dist
+
+logger = logging.getLogger(__name__)
 
 _GROUPS = {}
 
@@ -104,6 +108,7 @@ def ulysses_attention(ops, qkv, out, d, kv_map, scale, group, p, produce, consum
         o    [β'·T][p][Sl·HpD]   -> send2 [p][β'·T][Sl·HpD]      (then all-to-all)
         recv2 [p][n][HpD]        -> out   [n][p·HpD]             heads gather
     """
+    _log_path("NCCL all_to_all_single with swap01 pack / unpack")
     Sl, H, D, C = d.S, d.H, d.D, d.C
     Hp = H // p
     HpD = Hp * D
@@ -170,8 +175,10 @@ def peer_exchange_available(like: torch.Tensor, group) -> bool:
             t = symm.empty(1024, dtype=torch.uint8, device=like.device)
             symm.rendezvous(t, group.group_name)
             _SYMM_OK = True
-        except Exception:                                 # noqa: BLE001 - any failure means "not available here"
+        except Exception as e:                            # noqa: BLE001 - any failure means "not available here"
             _SYMM_OK = False
+            logger.warning("symmetric memory unavailable (%s: %s): sequence parallelism falls back to the NCCL "
+                           "all-to-all path", type(e).__name__, e)
         flag = torch.tensor([1 if _SYMM_OK else 0], device=like.device)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)      # all ranks take the same path
         _SYMM_OK = bool(flag.item())
@@ -188,6 +195,21 @@ def symm_buffer(tag, shape, like, group):
         hdl = symm.rendezvous(t, group.group_name)
         ent = _SYMM[key] = (t, hdl, [int(a) for a in hdl.buffer_ptrs])
     return ent
+
+
+_PATH_LOGGED = set()
+
+
+def _log_path(what):
+    """One line per process and path: which exchange the sequence-parallel attention takes."""
+    if what not in _PATH_LOGGED:
+        _PATH_LOGGED.add(what)
+        logger.info("sequence-parallel exchange: %s", what)
+
+
+def exchange_path() -> str:
+    """The exchange path(s) taken so far in this process (bench.py prints it in ``config``)."""
+    return "; ".join(sorted(_PATH_LOGGED)) or "none yet"
 
 
 stats = {"fused_qkv_scatter": 0, "fused_out_scatter": 0, "scatter_kernel": 0}     # which exchange ran (tests check the path taken)
@@ -220,7 +242,9 @@ def ulysses_attention_peer(ops, qkv, ao_sym, d, kv_map, scale, group, p, rank, p
     rows = slice(0, d.N)
     ident = lambda m: m                                   # noqa: E731
     full, hdl_f, ptrs_f = symm_buffer("full", (BT * p * Sl, 3 * HpD), qkv, group)
-    fused = _fused_scatter(ops, qkv, D, C, p)
+    fused = _fused_scatter(ops, qkv, D, C, p) and getattr(produce, "fusable", True)
+    _log_path("fused GEMM / attention epilogue scatter over NVLink peer memory" if fused else
+              "scatter kernels over NVLink peer memory")
     if fused:
         # the qkv projection's epilogue stores every head group straight into its owner's [β·T, S, 3, Hp·D] buffer:
         # GEMM and all-to-all are one kernel, the NVLink writes ride under the MMAs

@@ -346,7 +346,7 @@ class MagicDriveSTDiT3(PreTrainedModel):
 
         def cast(t):     # callers hand conditions in the model dtype (inference_magicdrive.py:345-358); be lenient
             return t.to(dtype) if isinstance(t, torch.Tensor) and t.is_floating_point() else t
-        cams, rel_pos, maps = cast(cams), cast(rel_pos), cast(maps)
+        y, cams, rel_pos, maps = cast(y), cast(cams), cast(rel_pos), cast(maps)
         drop_cond_mask, drop_frame_mask = cast(drop_cond_mask), cast(drop_frame_mask)
         if bbox is not None:
             bbox = {k_: cast(v_) for k_, v_ in bbox.items()}
@@ -416,7 +416,9 @@ class MagicDriveSTDiT3(PreTrainedModel):
         C, NH = self.hidden_size, self.num_heads
         x = x.to(dtype).contiguous()
         timestep = timestep.to(dtype)
-        y = y.to(dtype)
+        # (y keeps the caller's tensor: the condition cache is keyed on its identity — a cast here would make a new
+        # tensor, and a cache miss, every step whenever the text encoder's dtype differs from the model's; the cast
+        # happens inside _conditions, next to cams / rel_pos / maps)
         assert x.shape[1] == self.in_channels * NC
 
         # --- geometry (P2/P3) ---
@@ -529,7 +531,10 @@ class MagicDriveSTDiT3(PreTrainedModel):
             if i < self.control_depth and self.control_blocks_t is not None:
                 self.control_blocks_t[i].run(ops, xc, ws, d, mods["control_blocks_t"][i], None,
                                              ykv.get(f"control_blocks_t.{i}"), ctx, skip_into=xb)
-            if xi is not None and self.base_blocks_t is not None and self.brushnet_blocks_t is not None:
+            # (reference: below control_depth the brushnet temporal block runs whenever it exists,
+            #  magicdrive_stdit3.py:1766-1781; above it only together with the base temporal blocks, :1812-1842)
+            if xi is not None and self.brushnet_blocks_t is not None and (
+                    i < self.control_depth or self.base_blocks_t is not None):
                 self.brushnet_blocks_t[i].run(ops, xi, ws, d, mods["brushnet_blocks_t"][i], None,
                                               ykv.get(f"brushnet_blocks_t.{i}"), ctx, skip_into=xb)
 

@@ -155,11 +155,12 @@ def test_temporal_attention(dtype, T, D):
 
 
 @pytest.mark.parametrize("T,H,D", [(9, 16, 72), (13, 6, 64), (17, 16, 72), (17, 3, 72), (24, 8, 64), (32, 16, 64),
-                                   (32, 4, 40)])
+                                   (32, 4, 40), (33, 16, 72), (61, 16, 72), (61, 6, 64), (100, 2, 72)])
 def test_temporal_attention_long_clips(T, H, D):
     """8 < T <= 32 in bf16: the head-group staged kernel (one column x <= 8 heads per CTA; 65 pixel frames -> T = 17);
-    the last case has a head too narrow for the old in-slice probability table."""
-    dtype, B, S = torch.bfloat16, 2, 37
+    (32, 4, 40) has a head too narrow for the old in-slice probability table; T = 33 / 61 are the reference's 129-frame
+    and "full" 241-frame inference configs (32 < T <= 128: same staging, scalar phases)."""
+    dtype, B, S = torch.bfloat16, 2, (37 if T <= 32 else 11)
     qkv = rnd(B * T * S, 3 * H * D, dtype=dtype, seed=T)
     ang = torch.arange(T, dtype=torch.float32)[:, None] * (1.0 / 10000 ** (torch.arange(0, D, 2).float() / D))[None]
     ang = ang.repeat_interleave(2, dim=-1).to(DEV)
