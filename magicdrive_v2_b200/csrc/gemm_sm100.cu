@@ -69,8 +69,13 @@ struct Params {
   float eps;
 };
 
-template <int BN, int HD>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+// MC = CTA pairs per cluster.  MC = 2 (cluster of four): the two pairs compute N-ADJACENT tiles of the same 256 rows and
+// share the A operand through TMA multicast — each of the four CTAs fetches 64 of the 128 A rows it needs and
+// multicasts them to the CTA of the other pair that needs the same rows.  Why: with one pair per cluster every CTA pulls
+// (128 + BN/2) x 128 B per k-block through the L2 -> SM fabric, 64 / 75 / 89 B per clock and SM at full tensor rate for
+// BN = 256 / 192 / 144; sharing A brings that to 47 / 52 / 59 B/clk/SM.  (Experiment, off by default: see launch().)
+template <int BN, int HD, int MC>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                   const Params p) {
   using C = Cfg<BN, HD>;
@@ -86,9 +91,11 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_ctarank();              // 0 = leader (issues the pair's MMAs)
-  const int64_t pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
-  const int n_tiles_n = p.N / BN;
+  const uint32_t crank = cluster_ctarank();
+  const uint32_t rank = crank & 1;                      // within the pair: 0 = leader (issues the pair's MMAs)
+  const uint32_t q = crank >> 1;                        // pair within the cluster: N tile n_super·MC + q
+  const int64_t pair = blockIdx.x / (2 * MC), n_pairs = gridDim.x / (2 * MC);      // cluster index / clusters
+  const int n_tiles_n = p.N / BN / MC;                  // cluster tiles along N (MC adjacent BN-wide tiles each)
   const int64_t n_tiles_m = (p.M + 2 * BM - 1) / (2 * BM);
   const int64_t n_tiles = n_tiles_m * n_tiles_n;
   const int n_kb = p.K / BK;
@@ -98,7 +105,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     prefetch_tmap(&tmap_w);
     for (int i = 0; i < C::STAGES; ++i) {
       mbar_init(&full[i], 1);
-      mbar_init(&empty[i], 1);
+      mbar_init(&empty[i], MC);                         // one commit per pair that reads (or multicasts into) the stage
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
@@ -125,12 +132,18 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       uint32_t phase = 0;
       for (int64_t tile = pair; tile < n_tiles; tile += n_pairs) {
         const int m0 = (int)(tile / n_tiles_n) * 2 * BM + (int)rank * BM;
-        const int n0 = (int)(tile % n_tiles_n) * BN + (int)rank * (BN / 2);
+        const int n0 = ((int)(tile % n_tiles_n) * MC + (int)q) * BN + (int)rank * (BN / 2);
         for (int kb = 0; kb < n_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::STAGE_BYTES;
           if (rank == 0) mbar_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
-          tma_load_2d_pair(sa, &tmap_a, &full[stage], kb * BK, m0);
+          if constexpr (MC == 1) {
+            tma_load_2d_pair(sa, &tmap_a, &full[stage], kb * BK, m0);
+          } else {
+            // rows [q·64, q·64 + 64) of this CTA's 128 A rows, to itself and to the same-rank CTA of the other pair
+            tma_load_2d_pair_mc(sa + q * (A_BYTES / MC), &tmap_a, &full[stage], kb * BK, m0 + (int)q * (BM / MC),
+                                (uint16_t)(0x5u << rank));
+          }
           tma_load_2d_pair(sa + A_BYTES, &tmap_w, &full[stage], kb * BK, n0);
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
@@ -156,10 +169,10 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)
             umma_bf16_ss_pair(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
-          umma_commit_pair(&empty[stage]);
+          umma_commit_mc(&empty[stage], (uint16_t)((1u << (2 * MC)) - 1));     // every CTA of the cluster
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit_pair(&tfull[acc]);
+        umma_commit_mc(&tfull[acc], (uint16_t)(3u << (2 * q)));                 // the two CTAs of this pair
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -186,7 +199,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const bool has_res = HD == 0 && ep.res != nullptr, has_gate = HD == 0 && ep.gate_mod != nullptr;
     for (int64_t tile = pair; tile < n_tiles; tile += n_pairs) {
       const int64_t m0 = (tile / n_tiles_n) * 2 * BM + (int64_t)rank * BM;
-      const int n0 = (int)(tile % n_tiles_n) * BN;
+      const int n0 = ((int)(tile % n_tiles_n) * MC + (int)q) * BN;
       const int64_t r0 = m0 + quarter * 32;          // first row of this warp
       {  // per-row epilogue context, once per tile (64-bit divisions stay out of the inner loops)
         const int64_t gr = r0 + lane;
@@ -416,29 +429,69 @@ int mdv2_make_tmap_3d_heads(CUtensorMap* out, const void* ptr, uint64_t rows, ui
 }
 
 namespace {
-template <int BN, int HD>
-int launch(const CUtensorMap& ta, const CUtensorMap& tw, const Params& p, cudaStream_t st) {
+template <int BN, int HD, int MC>
+int launch_mc(const CUtensorMap& ta, const CUtensorMap& tw, const Params& p, cudaStream_t st) {
   using C = Cfg<BN, HD>;
+  auto kern = gemm_sm100_kernel<BN, HD, MC>;
   static PerDeviceFlag configured_flag; bool& configured = configured_flag.here();
+  static int max_clusters[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2 * MC;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = C::SMEM;
+  cfg.stream = st;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_sm100_kernel<BN, HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
     if (e != cudaSuccess) {
       mdv2_set_error("gemm_sm100: cannot set %d B dynamic smem: %s", C::SMEM, cudaGetErrorString(e));
       return MDV2_ECUDA;
     }
+    int n = mdv2_num_sms() / (2 * MC);
+    if (MC > 1) {                                      // clusters of four do not tile every GPC: ask the driver
+      cfg.gridDim = dim3(2 * MC * n);
+      int got = 0;
+      if (cudaOccupancyMaxActiveClusters(&got, kern, &cfg) == cudaSuccess && got > 0) n = got;
+      else cudaGetLastError();
+    }
+    max_clusters[dev & 63] = n;
     configured = true;
   }
-  const int64_t tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * (p.N / BN);
-  int64_t pairs = mdv2_num_sms() / 2;
+  const int64_t tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * (p.N / BN / MC);
+  int64_t clusters = max_clusters[dev & 63];
   static const int forced_pairs = [] {                 // tuning hook (tools/gemm_pairs_probe.py)
     const char* e = getenv("MDV2_GEMM_PAIRS");
     return e ? atoi(e) : 0;
   }();
-  if (forced_pairs > 0 && forced_pairs < pairs) pairs = forced_pairs;
-  const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
-  gemm_sm100_kernel<BN, HD><<<grid, NUM_THREADS, C::SMEM, st>>>(ta, tw, p);
+  if (forced_pairs > 0 && forced_pairs / MC < clusters) clusters = forced_pairs / MC > 0 ? forced_pairs / MC : 1;
+  cfg.gridDim = dim3((unsigned)(2 * MC * (tiles < clusters ? tiles : clusters)));
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tw, p);
+  if (e != cudaSuccess) {
+    mdv2_set_error("gemm_sm100: launch failed: %s", cudaGetErrorString(e));
+    return MDV2_ECUDA;
+  }
   MDV2_CHECK_LAUNCH("gemm_sm100");
   return MDV2_OK;
+}
+
+// pairs per cluster: one.  MDV2_GEMM_MC=2 selects the A-multicast clusters of four where the N tiles pair up — measured
+// (profiles/yardstick_gemm_r02.txt): +7 % per SM, but the driver places only 33 such clusters (132 of 148 SMs: GPCs of
+// 18 SMs do not tile by four), so every flavour is 3-5 % slower overall (the qkv flavour 22 %)
+template <int BN, int HD>
+int launch(const CUtensorMap& ta, const CUtensorMap& ta_mc, const CUtensorMap& tw, const Params& p, cudaStream_t st) {
+  static const int mc = [] {
+    const char* e = getenv("MDV2_GEMM_MC");
+    return e ? atoi(e) : 1;
+  }();
+  if (mc == 2 && (p.N / BN) % 2 == 0) return launch_mc<BN, HD, 2>(ta_mc, tw, p, st);
+  return launch_mc<BN, HD, 1>(ta, tw, p, st);
 }
 
 int pick_bn(int N, const RmsArgs* rms) {
@@ -475,8 +528,10 @@ int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void
                    (!ep.res || ((uintptr_t)ep.res % 16 == 0 && ep.ldr % 8 == 0)),
                "gemm_sm100: operands must be 16-byte aligned");
   const int bn = pick_bn(N, rms);
-  CUtensorMap ta, tw;
+  CUtensorMap ta, ta_mc, tw;
   int rc = mdv2_make_tmap_2d(&ta, a, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BM, BK);
+  if (rc) return rc;
+  rc = mdv2_make_tmap_2d(&ta_mc, a, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BM / 2, BK);     // 64-row boxes (multicast)
   if (rc) return rc;
   rc = mdv2_make_tmap_2d(&tw, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)bn / 2, BK);
   if (rc) return rc;
@@ -508,13 +563,13 @@ int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void
   p.n_k = rms ? rms->n_k : 0;
   p.eps = rms ? rms->eps : 0.f;
   switch (bn) {
-    case 256: return launch<256, 0>(ta, tw, p, st);
-    case 192: return launch<192, 0>(ta, tw, p, st);
-    case 64: return launch<64, 0>(ta, tw, p, st);
-    case 144: return launch<144, 72>(ta, tw, p, st);
+    case 256: return launch<256, 0>(ta, ta_mc, tw, p, st);
+    case 192: return launch<192, 0>(ta, ta_mc, tw, p, st);
+    case 64: return launch<64, 0>(ta, ta_mc, tw, p, st);
+    case 144: return launch<144, 72>(ta, ta_mc, tw, p, st);
     case 128:
-      if (rms && rms->wq) return launch<128, 64>(ta, tw, p, st);
-      return launch<128, 0>(ta, tw, p, st);
+      if (rms && rms->wq) return launch<128, 64>(ta, ta_mc, tw, p, st);
+      return launch<128, 0>(ta, ta_mc, tw, p, st);
   }
   MDV2_REQUIRE(false, "gemm_sm100: no tile for N=%d", N);
 }

@@ -10,7 +10,7 @@ for n in ${NS:-8 4 2}; do
 import json
 try:
     d=json.loads(open("gpurun_out/bench_n$n.json").read().strip().splitlines()[-1])
-    print("N=$n", d["ms_per_step"], "e2e", d["e2e"]["value"], "launches", d["gpu_launches"], d["clocks"])
+    print("N=$n", d["ms_per_step"], "sp_parity", d.get("sp_parity_rel_l2"), "e2e", d["e2e"]["value"], "launches", d["gpu_launches"], d["clocks"])
     tot=0
     for k,v in d["kernels"].items(): print("  ",k,v["calls"],v["ms"],v["achieved"],v["unit"]); tot+=v["ms"]
     print("   kernel sum", tot)
