@@ -858,17 +858,19 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
       auto smem_long = [&](int g) {
         return (size_t)Tn * (3 * g * D * 2 + TA_PAD) + 16 + (scalar ? (size_t)g * Tn * Tp * 4 : 0);
       };
+      // (very long clips, T ~ 100: not even one head fits 75 KB — one head per CTA, up to 200 KB, one or two CTAs per SM)
       int HG = 0;
       for (int g = H < 8 ? H : 8; g >= 1; --g)
         if (H % g == 0 && smem_long(g) <= 75 * 1024) {
           HG = g;
           break;
         }
+      if (!HG && smem_long(1) <= 200 * 1024) HG = 1;
       const int64_t n_ctas = (int64_t)B * S * (HG ? H / HG : 0);
       if (HG && n_ctas <= 0x7fffffff) {
         static PerDeviceFlag configured_flag; bool& configured = configured_flag.here();
         if (!configured) {
-          cudaFuncSetAttribute(temporal_attn_smem_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024);
+          cudaFuncSetAttribute(temporal_attn_smem_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
           configured = true;
         }
         temporal_attn_smem_long_kernel<<<(unsigned)n_ctas, TA_THREADS, smem_long(HG), st>>>(
@@ -893,6 +895,8 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
       return MDV2_OK;
     }
   }
+  MDV2_REQUIRE(Tn <= 64, "temporal_attention: T=%d not taken by the staged kernels (alignment / size) and beyond the "
+               "register kernel's 64 frames", Tn);
   dim3 grid((unsigned)((n_warps + 3) / 4)), block(128);
   const int ppl = (D / 2 + 31) / 32;
 #define TA_CASE(TM, PP)                                                                                \
