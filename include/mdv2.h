@@ -123,6 +123,21 @@ int mdv2_attention_scatter(const void* q, int64_t ldq, const void* k, int64_t ld
                            const int32_t* kv_map, int n_sets, void* const* dst_ptrs, int n_dst, int rows_per_rank,
                            int64_t dst_ld, int dst_col, void* stream);
 
+/* mdv2_attention_scatter for callers that cannot allocate (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The running sum of the earlier K/V sets (`partial` of mdv2_attention_scatter, [n_seq·Lq, H·D] bf16) lives in a
+ * file-scope device array of MDV2_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit; the
+ * caller still passes inputs and destinations.  Returns MDV2_EINVAL when n_seq·Lq·H·D·2 bytes exceed the array.
+ * Calls no cudaMalloc / cudaFree / allocating routine.  All calls share the array (it keeps the last call's
+ * contents; the kernel overwrites what it reads, nothing needs clearing): calls that overlap on the GPU — two
+ * streams, or two threads — race on it; serialise them on one stream.  bf16, sm_100a only. */
+#define MDV2_STATIC_SCRATCH_BYTES (16 * 1024 * 1024)
+int64_t mdv2_static_scratch_bytes(void);
+int mdv2_attention_scatter_static(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                                  int n_seq, int Lq, int Lk, int H, int D, float scale, const int32_t* kv_map,
+                                  int n_sets, void* const* dst_ptrs, int n_dst, int rows_per_rank, int64_t dst_ld,
+                                  int dst_col, void* stream);
+
 /* Tail of one RFLOW sampling step (magicdrivedit/schedulers/rf/__init__.py:100-109) plus the head of the next
  * (:95 and the x.to(dtype) of magicdrive_stdit3.py:1041), fused into one pass:
  *   v = pred[n:] + guidance * (pred[:n] - pred[n:]);  z_out = z + v * dt[b]        (fp32, each op rounded separately)

@@ -46,13 +46,16 @@ _lib.mdv2_gemm_qkv_scatter.argtypes = [_vp, _i64, _vp, _i64, _vp, _i64, _i32, _i
                                        ctypes.POINTER(_vp), _i32, _i32, _i32, _vp]
 _lib.mdv2_attention_scatter.argtypes = [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _f32,
                                         _vp, _i32, ctypes.POINTER(_vp), _i32, _i32, _i64, _i32, _vp]
-for _f in ("mdv2_attention_scatter", "mdv2_gemm_qkv_scatter", "mdv2_cfg_euler_step", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention", "mdv2_temporal_attention", "mdv2_patchify",
+_lib.mdv2_attention_scatter_static.argtypes = [_vp, _i64, _vp, _i64, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _f32, _vp,
+                                               _i32, ctypes.POINTER(_vp), _i32, _i32, _i64, _i32, _vp]
+_lib.mdv2_static_scratch_bytes.restype = _i64
+for _f in ("mdv2_attention_scatter_static", "mdv2_attention_scatter", "mdv2_gemm_qkv_scatter", "mdv2_cfg_euler_step", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention", "mdv2_temporal_attention", "mdv2_patchify",
            "mdv2_unpatchify", "mdv2_swap01", "mdv2_scatter_runs"):
     getattr(_lib, _f).restype = _i32
 
 EXPORTS = ("mdv2_version", "mdv2_last_error", "mdv2_last_kernel", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention",
            "mdv2_temporal_attention", "mdv2_patchify", "mdv2_unpatchify", "mdv2_swap01", "mdv2_scatter_runs", "mdv2_cfg_euler_step", "mdv2_gemm_qkv_scatter",
-           "mdv2_attention_scatter")
+           "mdv2_attention_scatter", "mdv2_attention_scatter_static", "mdv2_static_scratch_bytes")
 
 # kernel-launch counter (bench.py reports it as gpu_launches); +1 per C-ABI call that launches
 launches = 0
@@ -346,3 +349,23 @@ def attention_scatter(q, k, v, partial, n_seq, Lq, Lk, H, D, scale, dst_ptrs, ro
            "mdv2_attention_scatter")
     _t1(e0, "[spatial self + cross-view]", 4.0 * n_seq * Lq * Lk * H * D * n_sets,
         (2 * q.shape[0] + 2 * n_sets * n_seq * Lk) * H * D * q.element_size())
+
+
+def static_scratch_bytes() -> int:
+    return int(_lib.mdv2_static_scratch_bytes())
+
+
+def attention_scatter_static(q, k, v, n_seq, Lq, Lk, H, D, scale, dst_ptrs, rows_per_rank, dst_ld, dst_col, kv_map=None):
+    """``attention_scatter`` without a caller-owned ``partial`` buffer: the sum of earlier K/V sets lives in the
+    library's static device array (``static_scratch_bytes()``); allocates nothing.  Calls that overlap on the GPU
+    race on that array."""
+    pq, ldq = _rows2d(q)
+    pk, ldk = _rows2d(k)
+    pv, ldv = _rows2d(v)
+    n_sets = 1 if kv_map is None else kv_map.shape[1]
+    pm = _ptr(kv_map, torch.int32) if kv_map is not None else None
+    n = len(dst_ptrs)
+    arr = (_vp * n)(*[_vp(int(a)) for a in dst_ptrs])
+    _check(_lib.mdv2_attention_scatter_static(pq, ldq, pk, ldk, pv, ldv, n_seq, Lq, Lk, H, D, float(scale), pm, n_sets,
+                                              arr, n, rows_per_rank, dst_ld, dst_col, _stream()),
+           "mdv2_attention_scatter_static")
