@@ -30,6 +30,20 @@ __device__ __forceinline__ long long clk64() {
   return t;
 }
 
+__device__ __forceinline__ long long gtime_ns() {
+  long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)::"memory");
+  return t;
+}
+__device__ __forceinline__ uint32_t smid() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(r));
+  return r;
+}
+// per-CTA life line behind the per-warp timeline (TRACE builds): 8 int64 per CTA —
+// 0 start, 1 SM id, 2 first S tile seen by softmax warp 0, 3 last P of the CTA stored (warp 0), 4 O complete, 5 end
+constexpr int TRACE_CTA_OFF = 20 * TRACE_STEPS * TRACE_EV, TRACE_CTA_EV = 8;
+
 __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));

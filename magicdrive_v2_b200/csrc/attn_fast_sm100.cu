@@ -99,6 +99,16 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   const int q_row0 = qp * QT * BMQ;                     // first query row of this CTA within the sequence
   const int n_qt = (q_row0 + BMQ < p.Lq) ? 2 : 1;       // the second tile may lie entirely past Lq
   const bool tracing = TRACE && p.trace != nullptr && qp == 3 && h == 1 && seq == (int)gridDim.z / 2;
+  long long* cta_line = nullptr;                        // TRACE: life line of EVERY CTA (global timer, ns)
+  if constexpr (TRACE) {
+    if (p.trace != nullptr)
+      cta_line = p.trace + TRACE_CTA_OFF +
+                 (int64_t)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) * TRACE_CTA_EV;
+    if (cta_line && threadIdx.x == 0) {
+      cta_line[0] = gtime_ns();
+      cta_line[1] = smid();
+    }
+  }
   auto mark = [&](int j, int ev) {
     if constexpr (TRACE) {
       if (tracing && lane == 0 && j < TRACE_STEPS) p.trace[(warp * TRACE_STEPS + j) * TRACE_EV + ev] = clk64();
@@ -327,6 +337,9 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           mbar_wait(&s_full[t * 2 + hf], cnt & 1);
           tc_fence_after();
           mark(cnt, 0);
+          if constexpr (TRACE) {
+            if (cta_line && warp == 0 && lane == 0 && cnt == 0) cta_line[2] = gtime_ns();
+          }
           const int kv_left = kt == n_kt - 1 ? p.Lk - kt * BNK - hf * HB : HB;   // keys of this half that exist
           // two 32-key chunks; P chunk q goes to columns 16q..16q+15 of the half, over scores already in registers.
           // (Tried: four 16-key chunks double-buffered through registers so that the tcgen05.ld of the next chunk
@@ -369,6 +382,9 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           __syncwarp();
           if (lane == 0) mbar_arrive(&p_full[t * 2 + hf]);
           mark(cnt, 3);
+          if constexpr (TRACE) {
+            if (cta_line && warp == 0 && lane == 0) cta_line[3] = gtime_ns();
+          }
         }
         jg += n_kt;
         // end of the pass: the row sum of both halves, and the CTA-wide verdict
@@ -387,10 +403,25 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           continue;
         }
         // normalise, round to bf16, add to what earlier sets left in `out`: this warp takes half of the columns
+        // earlier sets' partial sums of this row: all loads go out NOW and fly under the wait for O.  (They used to sit
+        // behind the stores of the previous unit — same pointer, so the compiler kept load / add / store strictly in
+        // order: five dependent global round trips, 8.5 us from "O complete" to CTA exit instead of 2.3,
+        // profiles/attn_cta_lifeline_r02.txt.)
+        constexpr int NU = DP / 16;                      // 8-column units per warp
+        uint4 prev[NU];
+        if (set > 0 && q_idx < p.Lq) {
+#pragma unroll
+          for (int u = 0; u < NU; ++u) {
+            const int d = hf * (DP / 2) + u * 8;
+            if (d < p.D) prev[u] = *reinterpret_cast<const uint4*>(orow + d);
+          }
+        }
         mbar_wait(&o_full[t], (uint32_t)((pass - 1) & 1));
         tc_fence_after();
+        if constexpr (TRACE) {
+          if (cta_line && warp == 0 && lane == 0) cta_line[4] = gtime_ns();
+        }
         const float inv = 1.f / l_row;
-        constexpr int NU = DP / 16;                      // 8-column units per warp
         uint32_t r[NU * 8];
 #pragma unroll
         for (int u = 0; u < NU; ++u) tmem_ld_x8(o_addr + hf * (DP / 2) + u * 8, r + u * 8);
@@ -406,10 +437,10 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
               Vec16<bf16> o;
               o.pack(f);
               if (set > 0) {
-                Vec16<bf16> prev;
-                prev.raw = *reinterpret_cast<const uint4*>(orow + d);
+                Vec16<bf16> pv;
+                pv.raw = prev[u];
                 float gg[8], a[8];
-                prev.unpack(gg);
+                pv.unpack(gg);
                 o.unpack(a);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) a[i] += gg[i];
@@ -429,6 +460,9 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   if (warp == MMA_WARP0) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+  if constexpr (TRACE) {
+    if (cta_line && threadIdx.x == 0) cta_line[5] = gtime_ns();
   }
 }
 

@@ -495,6 +495,8 @@ extern "C" void mdv2_debug_attn_trace(void* buf) { g_attn_trace = (long long*)bu
 
 int mdv2_attention_fast_launch(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p,
                                int n_seq, int D, bool trace, cudaStream_t st);
+int mdv2_attention_pers_launch(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p,
+                               int n_seq, int D, bool trace, cudaStream_t st);
 
 bool mdv2_attention_sm100_supported(int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int Lq, int Lk, int H, int D,
                                     int n_sets) {
@@ -555,6 +557,11 @@ int mdv2_attention_sm100(const void* q, int64_t ldq, const void* k, int64_t ldk,
     const char* e = getenv("MDV2_ATTN_FAST");
     return e ? atoi(e) : 1;
   }();
+  static const int persist = [] {                        // MDV2_ATTN_PERSIST=1: the persistent kernel (attn_pers_sm100.cu), opt-in
+    const char* e = getenv("MDV2_ATTN_PERSIST");
+    return e ? atoi(e) : 0;
+  }();
+  if (bnk == 128 && fast && persist) return mdv2_attention_pers_launch(tq, tk, tv, p, n_seq, D, g_attn_trace != nullptr, st);
   if (bnk == 128 && fast) return mdv2_attention_fast_launch(tq, tk, tv, p, n_seq, D, g_attn_trace != nullptr, st);
   if (D == 72 && bnk == 128 && g_attn_trace) {
     if (pf == 0) return launch_attn<80, 128, 0, true>(tq, tk, tv, p, n_seq, st);

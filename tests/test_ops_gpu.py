@@ -257,6 +257,19 @@ def test_attention_tcgen05_xl_shape():
     assert _attn_case(3, 1600, 1600, 16, 72) < ATTN_TOL            # 12.5 key tiles: the last tile's second half is skipped
 
 
+def test_attention_tcgen05_persistent_many_items_per_cta():
+    """More work items than SMs: every CTA of the persistent kernel walks several (sequence, head, query-tile pair)
+    items, so Q / K / V of the next item are prefetched and its first score tile is issued behind the last P·V of the
+    current one — with two K/V sets, lone last query tiles (600 = 2·256 + 88) and a one-half last key tile."""
+    assert _attn_case(12, 600, 600, 16, 72, kv="xview") < ATTN_TOL      # 576 items, 2 sets, lone tile, 5 key tiles (88 -> 2 halves)
+    assert _attn_case(10, 576, 576, 16, 72, kv="xview") < ATTN_TOL      # last key tile holds 64 keys: one half-step
+    assert _attn_case(40, 200, 130, 8, 64, kv="cross") < ATTN_TOL       # 320 items of two key tiles, the last with 2 keys
+    assert _attn_case(9, 300, 128, 16, 72, kv="cross") < ATTN_TOL       # one key tile per pass
+    # overflow of the fixed reference in most items: the careful second phase re-runs them, several per CTA
+    assert _attn_case(8, 1000, 1000, 16, 72, q_gain=20.0) < ATTN_TOL
+    assert _attn_case(6, 600, 600, 16, 72, kv="xview", q_gain=20.0) < ATTN_TOL
+
+
 @pytest.mark.parametrize("gain", [6.0, 20.0])
 def test_attention_tcgen05_rescale_path(gain):
     """Scores with a spread of tens of log2 units: the running maximum keeps outgrowing the lazy-rescale
