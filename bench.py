@@ -364,6 +364,20 @@ def measure(wl_name, args, rank, world, device, pk, do_profile=True):
     model.cache_conditions = True
     step()
     ms_cached = timed_steps(step, args.steps, dist_on) / args.steps
+    # ... and the same step replayed as ONE CUDA graph: no Python, no launch path, no tensor-map encoding
+    ms_graph, graph_note = None, None
+    try:
+        gstep = model.capture_step(**inp)
+        gx, gt = inp["x"].clone(), inp["timestep"].clone()
+        ref = step()
+        got = gstep(gx, gt)
+        torch.cuda.synchronize()
+        assert torch.equal(ref, got), "the replayed graph and the eager step disagree"
+        ms_graph = timed_steps(lambda: gstep(gx, gt), args.steps, dist_on) / args.steps
+        del gstep, ref, got
+    except Exception as e:                              # noqa: BLE001 - reported, never fatal for the bench line
+        graph_note = f"{type(e).__name__}: {str(e)[:160]}"
+        torch.cuda.synchronize()
     model.cache_conditions = False
     model.clear_condition_cache()
 
@@ -395,7 +409,7 @@ def measure(wl_name, args, rank, world, device, pk, do_profile=True):
     torch.cuda.synchronize()
     del model
     torch.cuda.empty_cache()
-    return dict(ms_step=ms_step, ms_cached=ms_cached, ms_e2e=ms_e2e, h2d=h2d, d2h=d2h, launches=launches,
+    return dict(ms_step=ms_step, ms_cached=ms_cached, ms_graph=ms_graph, graph_note=graph_note, ms_e2e=ms_e2e, h2d=h2d, d2h=d2h, launches=launches,
                 clocks=clocks, kernels=kernels, wl=wl, sp_parity=sp_parity, finite=finite)
 
 
@@ -468,6 +482,8 @@ def main():
         f2 = algorithmic_flops(2, 6, 5, c2["tokens_per_frame"], L)
         secondary = dict(config=c2, value=1e3 / r2["ms_step"], unit=UNIT, ms_per_step=r2["ms_step"],
                          value_conditions_cached=1e3 / r2["ms_cached"],
+                         value_cuda_graph=(1e3 / r2["ms_graph"]) if r2["ms_graph"] else None,
+                         cuda_graph_note=r2["graph_note"],
                          e2e=dict(value=1e3 / r2["ms_e2e"], unit=UNIT, h2d_bytes_per_step=r2["h2d"],
                                   d2h_bytes_per_step=r2["d2h"]),
                          gpu_launches=r2["launches"], algorithmic_tflop_per_step=f2["total"] / 1e12,
@@ -505,6 +521,8 @@ def main():
                          d2h_bytes_per_step=res["d2h"]),
                 gpu_launches=res["launches"], clocks=res["clocks"], roofline=roofline, kernels=ktab,
                 value_conditions_cached=1e3 / res["ms_cached"],
+                value_cuda_graph=(1e3 / res["ms_graph"]) if res["ms_graph"] else None,
+                cuda_graph_note=res["graph_note"],
                 algorithmic_tflop_per_step=fl["total"] / 1e12,
                 step_tflops_per_gpu=step_tf, step_frac_of_bf16_sustained=step_tf / pk["tf_sustained"],
                 step_frac_of_bf16_burst=step_tf / pk["tf_burst"])

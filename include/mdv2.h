@@ -41,6 +41,14 @@ int mdv2_ln_modulate(const void* x, void* out, const float* mod, int64_t n_rows,
                      int k_shift, int k_scale, int T, int S, int NC, float eps, int dtype,
                      void* stream);
 
+/* adaLN modulation tables of all blocks in one pass: out[n][bt][k][c] (fp32) = round_dtype(tables[n][k][c] +
+ * tsel[bt][k][c or 0]); tables = the blocks' stacked scale_shift_table parameters [n, K, C], tsel = the x_mask-selected
+ * timestep vector of every (b, t) frame, [BT, K, Ct] with Ct = C or 1 (the scalar modulation of the cross-view branch).
+ * Replaces the per-block `self.scale_shift_table[None] + t.reshape(B, 6, -1)` (+ the t0 copy and t_mask_select) of
+ * MultiViewSTDiT3Block.forward, stdit3.py:213-221,288-296, and `scale_shift_table_mva[None] + t_mlp[:, :3]`, :303-305. */
+int mdv2_adaln_tables(const void* tables, const void* tsel, float* out, int n, int BT, int K, int C, int Ct, int dtype,
+                      void* stream);
+
 /* out[M,N] = epilogue(a[M,K] · w[N,K]^T):  v = acc + bias_scale·bias ; optional per-head RMSNorm
  * (columns [0,n_q) with rms_q, [n_q,n_q+n_k) with rms_k, head_dim wide) ; optional tanh-GELU ;
  * optional gate (fp32 table row, index k_gate) ; optional residual (row r, or mapped row

@@ -210,3 +210,61 @@ int mdv2_qk_rmsnorm(void* qkv, int64_t ld, int64_t M, int D, int n_q, int n_k, c
   MDV2_CHECK_LAUNCH("qk_rmsnorm");
   return MDV2_OK;
 }
+
+
+// ------------------------------------------------------------------------------------------------
+// adaLN modulation tables of ALL blocks in one pass:
+//   out[n][bt][k][c] (fp32) = round_T(tables[n][k][c] + tsel[bt][k][c or 0])
+// tables: the stacked scale_shift_table parameters [n, K, C]; tsel: the (x_mask-selected) timestep vector per (b, t)
+// frame, [BT, K, Ct] with Ct = C (6-row tables) or 1 (the scalar modulation of the cross-view branch).  The sum is
+// rounded to the model dtype like the reference's own add (bf16 + bf16 -> bf16) and widened for the kernels that read it.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void adaln_tables_kernel(const T* __restrict__ tables, const T* __restrict__ tsel, float* __restrict__ out,
+                                    int64_t total4, int BT, int KC4, int C4, int Ct) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (int64_t)gridDim.x * blockDim.x) {
+    const int kc = (int)(i % KC4);                        // (k, c/4)
+    const int64_t r = i / KC4;
+    const int bt = (int)(r % BT);
+    const int64_t n = r / BT;
+    const T* tp = tables + (n * KC4 + kc) * 4;
+    float tv[4];
+    if (Ct == 1) {
+      const float v = to_f(tsel[(int64_t)bt * (KC4 / C4) + kc / C4]);
+      tv[0] = tv[1] = tv[2] = tv[3] = v;
+    } else {
+      const T* sp = tsel + ((int64_t)bt * KC4 + kc) * 4;
+#pragma unroll
+      for (int e = 0; e < 4; ++e) tv[e] = to_f(sp[e]);
+    }
+    float4 o;
+    o.x = to_f(from_f<T>(to_f(tp[0]) + tv[0]));
+    o.y = to_f(from_f<T>(to_f(tp[1]) + tv[1]));
+    o.z = to_f(from_f<T>(to_f(tp[2]) + tv[2]));
+    o.w = to_f(from_f<T>(to_f(tp[3]) + tv[3]));
+    reinterpret_cast<float4*>(out)[i] = o;
+  }
+}
+
+extern "C" int mdv2_adaln_tables(const void* tables, const void* tsel, float* out, int n, int BT, int K, int C, int Ct,
+                                 int dtype, void* stream) {
+  if ((int64_t)n * BT * K * C == 0) return MDV2_OK;
+  MDV2_REQUIRE(n > 0 && BT > 0 && K > 0 && C > 0 && C % 4 == 0, "adaln_tables: bad shape n=%d BT=%d K=%d C=%d", n, BT, K, C);
+  MDV2_REQUIRE(Ct == C || Ct == 1, "adaln_tables: the timestep vector is [BT, K, C] or [BT, K, 1]");
+  MDV2_REQUIRE(dtype == 0 || dtype == 1, "adaln_tables: bad dtype %d", dtype);
+  MDV2_REQUIRE((uintptr_t)out % 16 == 0, "adaln_tables: output must be 16-byte aligned");
+  const int64_t total4 = (int64_t)n * BT * K * C / 4;
+  const int threads = 256;
+  int64_t blocks = (total4 + threads - 1) / threads;
+  const int64_t cap = (int64_t)mdv2_num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == 0)
+    adaln_tables_kernel<float><<<(unsigned)blocks, threads, 0, st>>>((const float*)tables, (const float*)tsel, out, total4, BT,
+                                                                    K * C / 4, C / 4, Ct);
+  else
+    adaln_tables_kernel<bf16><<<(unsigned)blocks, threads, 0, st>>>((const bf16*)tables, (const bf16*)tsel, out, total4, BT,
+                                                                   K * C / 4, C / 4, Ct);
+  MDV2_CHECK_LAUNCH("adaln_tables");
+  return MDV2_OK;
+}

@@ -30,6 +30,7 @@ _lib.mdv2_version.restype = _i32
 _lib.mdv2_last_error.restype = ctypes.c_char_p
 _lib.mdv2_last_kernel.restype = ctypes.c_char_p
 _lib.mdv2_ln_modulate.argtypes = [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _i32, _vp]
+_lib.mdv2_adaln_tables.argtypes = [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp]
 _lib.mdv2_gemm.argtypes = [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _f32, _vp, _i32, _i32,
                            _vp, _i64, _i64, _i64, _i32, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _f32, _i32, _i32, _vp]
 _lib.mdv2_attention.argtypes = [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _f32,
@@ -49,13 +50,13 @@ _lib.mdv2_attention_scatter.argtypes = [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i
 _lib.mdv2_attention_scatter_static.argtypes = [_vp, _i64, _vp, _i64, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _f32, _vp,
                                                _i32, ctypes.POINTER(_vp), _i32, _i32, _i64, _i32, _vp]
 _lib.mdv2_static_scratch_bytes.restype = _i64
-for _f in ("mdv2_attention_scatter_static", "mdv2_attention_scatter", "mdv2_gemm_qkv_scatter", "mdv2_cfg_euler_step", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention", "mdv2_temporal_attention", "mdv2_patchify",
+for _f in ("mdv2_adaln_tables", "mdv2_attention_scatter_static", "mdv2_attention_scatter", "mdv2_gemm_qkv_scatter", "mdv2_cfg_euler_step", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention", "mdv2_temporal_attention", "mdv2_patchify",
            "mdv2_unpatchify", "mdv2_swap01", "mdv2_scatter_runs"):
     getattr(_lib, _f).restype = _i32
 
 EXPORTS = ("mdv2_version", "mdv2_last_error", "mdv2_last_kernel", "mdv2_ln_modulate", "mdv2_gemm", "mdv2_attention",
            "mdv2_temporal_attention", "mdv2_patchify", "mdv2_unpatchify", "mdv2_swap01", "mdv2_scatter_runs", "mdv2_cfg_euler_step", "mdv2_gemm_qkv_scatter",
-           "mdv2_attention_scatter", "mdv2_attention_scatter_static", "mdv2_static_scratch_bytes")
+           "mdv2_attention_scatter", "mdv2_attention_scatter_static", "mdv2_static_scratch_bytes", "mdv2_adaln_tables")
 
 # kernel-launch counter (bench.py reports it as gpu_launches); +1 per C-ABI call that launches
 launches = 0
@@ -141,6 +142,20 @@ def _check(rc: int, name: str):
     if rc != 0:
         raise RuntimeError(f"{name} failed ({rc}): {_lib.mdv2_last_error().decode()}")
     launches += 1
+
+
+def adaln_tables(tables, tsel, out=None):
+    """fp32 ``[n, BT, K, C]`` = tables ``[n, K, C]`` + tsel ``[BT, K, C or 1]``, the sum rounded to the model dtype."""
+    n, K, C = tables.shape
+    BT, Ct = tsel.shape[0], tsel.shape[-1]
+    assert tables.is_contiguous() and tsel.is_contiguous() and tsel.shape[1] == K and tsel.dtype == tables.dtype
+    if out is None:
+        out = torch.empty(n, BT, K, C, dtype=torch.float32, device=tables.device)
+    e0 = _t0()
+    _check(_lib.mdv2_adaln_tables(_ptr(tables), _ptr(tsel), _ptr(out, torch.float32), n, BT, K, C, Ct, _dt(tables),
+                                  _stream()), "mdv2_adaln_tables")
+    _t1(e0, "", 0.0, out.numel() * 4 + tables.numel() * tables.element_size())
+    return out
 
 
 def ln_modulate(x, out, mod, k_shift, k_scale, geo, eps=1e-6):

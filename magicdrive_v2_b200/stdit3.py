@@ -388,13 +388,31 @@ class MagicDriveSTDiT3(PreTrainedModel):
     # ------------------------------------------------------------------------------------------
     # the denoising step
     # ------------------------------------------------------------------------------------------
-    def _mod_tables(self, blocks, attr, tsel, K, dtype):
-        """[n_blk, b·T, K, C] fp32 = table + (x_mask-selected) timestep vector, rounded like the
-        reference's bf16 add (magicdrive_stdit3.py:213-221).  tsel: [b, T, K, C] (or [b,T,K,1])."""
-        tab = torch.stack([getattr(blk, attr) for blk in blocks]).to(dtype)          # [n, K, C]
-        mod = (tab[:, None, None] + tsel[None].to(dtype)).float()
-        n, b, T = mod.shape[:3]
-        return mod.view(n, b * T, K, -1).contiguous()
+    def _stacked_tables(self, names, attr, dtype):
+        """The ``attr`` parameters of every block of the lists ``names``, stacked ``[n_total, K, C]`` in the model dtype
+        — built once and kept until a parameter changes — plus the slice of every list."""
+        lists = [(n, getattr(self, n)) for n in names if getattr(self, n, None) is not None]
+        params = [getattr(blk, attr) for _, blocks in lists for blk in blocks]
+        key = (dtype, tuple((p_.data_ptr(), p_._version) for p_ in params))
+        cache = self.__dict__.setdefault("_tab_cache", {})
+        hit = cache.get((names, attr))
+        if hit is None or hit[0] != key:
+            stacked = torch.stack([p_.detach() for p_ in params]).to(dtype).contiguous()
+            slices, o = {}, 0
+            for n, blocks in lists:
+                slices[n] = slice(o, o + len(blocks))
+                o += len(blocks)
+            hit = cache[(names, attr)] = (key, stacked, slices)
+        return hit[1], hit[2]
+
+    def _mod_tables(self, names, attr, tsel, dtype):
+        """{list name: [n_blk, b·T, K, C] fp32} = table + (x_mask-selected) timestep vector, rounded like the
+        reference's bf16 add (magicdrive_stdit3.py:213-221) — ONE libmdv2 launch for all the lists ``names``.
+        tsel: [b, T, K, C] (or [b, T, K, 1])."""
+        stacked, slices = self._stacked_tables(names, attr, dtype)
+        b, T, K = tsel.shape[:3]
+        mod = self.ops.adaln_tables(stacked, tsel.to(dtype).reshape(b * T, K, tsel.shape[-1]).contiguous())
+        return {n: mod[sl] for n, sl in slices.items()}
 
     @torch.no_grad()
     def forward(self, x, timestep, y, maps, bbox, cams, rel_pos, fps, height, width,
@@ -436,7 +454,12 @@ class MagicDriveSTDiT3(PreTrainedModel):
         Sl = s1 - s0
 
         base_size = round(S ** 0.5)
-        scale = (float(height[0]) * float(width[0])) ** 0.5 / self.input_sq_size
+        # (the reference reads height[0] / width[0] on the host every forward, magicdrive_stdit3.py:1113; the device ->
+        # host read is done once per pair of caller tensors, so a sampling loop — and a captured CUDA graph — has none)
+        hw_key = (id(height), height._version, id(width), width._version)
+        if getattr(self, "_hw_scale", (None,))[0] != hw_key:
+            self._hw_scale = (hw_key, (float(height[0]) * float(width[0])) ** 0.5 / self.input_sq_size, height, width)
+        scale = self._hw_scale[1]
         pos = self.pos_embed(dev, dtype, Hp, Wp, scale=scale, base_size=base_size)       # [S, C]
 
         # --- timestep embeddings (b rows; library GEMVs) ---
@@ -494,22 +517,29 @@ class MagicDriveSTDiT3(PreTrainedModel):
         tm6 = tm_sel.reshape(b, T, 6, C)
         tm3 = tm_sel[:, :, :3].reshape(b, T, 3, 1)
         tm6b = tm_sel_brush.reshape(b, T, 6, C)
-        mods = {name: self._mod_tables(getattr(self, name), "scale_shift_table",
-                                       tm6b if name.startswith("brushnet") else tm6, 6, dtype)
-                for name in self._BLOCK_LISTS if getattr(self, name, None) is not None}
-        mod_mva = self._mod_tables(self.base_blocks_s, "scale_shift_table_mva", tm3, 3, dtype)
-        mva_ctrl = mva_brush = None
-        if self.control_depth > 0 and not self.control_blocks_s[0].skip_cross_view:
-            mva_ctrl = self._mod_tables(self.control_blocks_s, "scale_shift_table_mva", tm3, 3, dtype)
-        if xi is not None and not self.brushnet_blocks_s[0].skip_cross_view:
-            mva_brush = self._mod_tables(self.brushnet_blocks_s, "scale_shift_table_mva",
-                                         tm_sel_brush[:, :, :3].reshape(b, T, 3, 1), 3, dtype)
+        main_lists = tuple(n for n in self._BLOCK_LISTS if not n.startswith("brushnet"))
+        mods = self._mod_tables(main_lists, "scale_shift_table", tm6, dtype)
+        mva_lists = ("base_blocks_s",) + (("control_blocks_s",) if self.control_depth > 0 and
+                                          not self.control_blocks_s[0].skip_cross_view else ())
+        mva = self._mod_tables(mva_lists, "scale_shift_table_mva", tm3, dtype)
+        mod_mva, mva_ctrl, mva_brush = mva["base_blocks_s"], mva.get("control_blocks_s"), None
+        if xi is not None:                                 # the third stream has its own time vector (SDE variant)
+            mods.update(self._mod_tables(tuple(n for n in self._BLOCK_LISTS if n.startswith("brushnet")),
+                                         "scale_shift_table", tm6b, dtype))
+            if not self.brushnet_blocks_s[0].skip_cross_view:
+                mva_brush = self._mod_tables(("brushnet_blocks_s",), "scale_shift_table_mva",
+                                             tm_sel_brush[:, :, :3].reshape(b, T, 3, 1), dtype)["brushnet_blocks_s"]
 
         ctx = _Ctx()
         ctx.L, ctx.y_frames = cnd["L"], cnd["y_frames"]
-        ctx.kv_map = indexmaps.cross_view_kv_map(mv_order_map, b, T, NC).to(dev)
-        ang = self.rope.angles(T, dtype, dev)                                          # [T, D]
-        ctx.rope_cos, ctx.rope_sin = ang.cos().float().contiguous(), ang.sin().float().contiguous()
+        # index map and RoPE tables: small, shape-keyed, kept on the device (no host -> device copy per step)
+        step_key = (tuple((k_, tuple(int(n_) for n_ in v_)) for k_, v_ in sorted(mv_order_map.items())), b, T, NC,
+                    dtype, str(dev), self.rope.freqs.data_ptr(), self.rope.freqs._version)
+        if getattr(self, "_step_tabs", (None,))[0] != step_key:
+            ang = self.rope.angles(T, dtype, dev)                                      # [T, D]
+            self._step_tabs = (step_key, indexmaps.cross_view_kv_map(mv_order_map, b, T, NC).to(dev),
+                               ang.cos().float().contiguous(), ang.sin().float().contiguous())
+        _, ctx.kv_map, ctx.rope_cos, ctx.rope_sin = self._step_tabs
         ctx.spatial_attention = self._spatial_attention
         ykv = cnd["y_kv"]
 
@@ -565,6 +595,10 @@ class MagicDriveSTDiT3(PreTrainedModel):
     # ------------------------------------------------------------------------------------------
     # sequence parallelism (Ulysses head-scatter over the spatial tokens; blocks.py:546-645)
     # ------------------------------------------------------------------------------------------
+    def capture_step(self, warmup=2, **inputs):
+        """-> ``GraphedStep``: this forward, with these (fixed) conditions, as a replayable CUDA graph."""
+        return GraphedStep(self, inputs, warmup=warmup)
+
     def _sp(self):
         from . import sp
         if not self.enable_sequence_parallelism:
@@ -599,6 +633,39 @@ class MagicDriveSTDiT3(PreTrainedModel):
     def _sp_gather_tokens(self, yo, d: Dims, p, group):
         from . import sp
         return sp.gather_tokens(yo, d, p, group)
+
+
+class GraphedStep:
+    """One denoising step of a sample as a CUDA graph (the reference launches ~4000 eager kernels per
+    step, schedulers/rf/__init__.py:82-113).  The conditions are fixed for the sample (encoded once, before the capture,
+    through the condition cache); every call refreshes the latent and the timestep in place and replays the ~1100
+    libmdv2 launches of the step without touching Python or the launch path.
+
+        step = model.capture_step(**inputs)          # inputs: the forward's keyword arguments, device tensors
+        v = step(x, timestep)                        # -> the same fp32 velocity tensor object every call
+    """
+
+    def __init__(self, model, inputs, warmup=2):
+        assert model.cache_conditions, "a captured step needs the condition cache (conditions are encoded once)"
+        self.model = model
+        self.static = dict(inputs)
+        self.static["x"] = inputs["x"].clone()
+        self.static["timestep"] = inputs["timestep"].clone()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):                      # warm-up off the capture: workspaces, kernel attributes,
+            for _ in range(warmup):                        # condition cache, symmetric buffers
+                model(**self.static)
+        torch.cuda.current_stream().wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.out = model(**self.static)
+
+    def __call__(self, x, timestep):
+        self.static["x"].copy_(x)
+        self.static["timestep"].copy_(timestep)
+        self.graph.replay()
+        return self.out
 
 
 def _build(cls, from_pretrained=None, force_huggingface=False, strict=True, **kwargs):

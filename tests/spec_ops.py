@@ -16,6 +16,14 @@ def _mod_rows(n_rows, geo, device):
     return (g // T // NC) * T + g % T
 
 
+def adaln_tables(tables, tsel, out=None):
+    r = (tables[:, None] + tsel[None]).float()               # the add rounds to the model dtype, like the reference's
+    if out is None:
+        return r.contiguous()
+    out.copy_(r)
+    return out
+
+
 def ln_modulate(x, out, mod, k_shift, k_scale, geo, eps=1e-6):
     xf = x.float()
     xn = F.layer_norm(xf, (xf.shape[-1],), eps=eps)

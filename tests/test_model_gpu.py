@@ -56,6 +56,55 @@ def test_native_library_is_the_path_that_runs():
     assert type(model).__mro__[0].__name__ == "MagicDriveSTDiT3" and type(model)._ops is ops
 
 
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2)])
+def test_condition_cache_on_the_real_model(dtype, tol):
+    """SURVEY §8 f1 on the GPU: with the condition / cross-attention K-V cache on, the second denoising step of a
+    sample (same condition tensors, a new latent and timestep) re-uses the encodings — fewer libmdv2 launches, the
+    cache entry untouched — and still matches the reference golden; changed conditions miss."""
+    from magicdrive_v2_b200 import ops
+    fix = load_golden("tiny_9f_first0.pt")
+    model, wl, kw = build_model("tiny_9f")
+    model = model.to("cuda", dtype)
+    model.cache_conditions = True
+    inp = synth.to_device(synth.make_inputs(wl, seed=fix["seed"], x_mask="first0", kw=kw), "cuda")
+    n0 = ops.launches
+    out1 = model(**inp)
+    n1 = ops.launches
+    entry = model._cond_cache[0][1]
+    other = dict(inp, x=inp["x"] * 0.5, timestep=inp["timestep"] * 0.25)     # the next step of the same sample
+    model(**other)
+    n2 = ops.launches
+    assert model._cond_cache[0][1] is entry                      # hit: nothing was re-encoded
+    assert n2 - n1 < n1 - n0                                     # ... and the kv_linear / map GEMMs did not run again
+    out2 = model(**inp)                                          # the first step again, now from the cache
+    torch.cuda.synchronize()
+    assert torch.equal(out1, out2)
+    assert rel_l2(out2.cpu(), fix["out"]) < tol
+    changed = dict(inp, y=inp["y"].clone())                      # another condition tensor: a miss, a new entry
+    out3 = model(**changed)
+    assert model._cond_cache[0][1] is not entry
+    assert torch.equal(out3, out1)
+    model.cache_conditions = False
+    out4 = model(**inp)
+    assert torch.equal(out4, out1)
+
+
+def test_captured_step_replays_the_eager_step():
+    """one denoising step as a CUDA graph — replays must be bit-identical to the eager forward for every
+    new latent / timestep, with the conditions encoded once."""
+    model, wl, kw = build_model("tiny_9f")
+    model = model.to("cuda", torch.bfloat16)
+    model.cache_conditions = True
+    inp = synth.to_device(synth.make_inputs(wl, seed=3, x_mask="first0", kw=kw), "cuda")
+    step = model.capture_step(**inp)
+    for i, (sx, st) in enumerate(((1.0, 1.0), (0.5, 0.25), (-2.0, 0.75))):
+        x, t = inp["x"] * sx, inp["timestep"] * st
+        want = model(**dict(inp, x=x, timestep=t)).clone()
+        got = step(x, t)
+        torch.cuda.synchronize()
+        assert torch.isfinite(got).all() and torch.equal(got, want), i
+
 BRUSH_CASES = [("brushnet_tiny_9f_first0_noca.pt", True), ("brushnet_tiny_9f_None_ca.pt", False),
                ("brushnet_tiny_9f_ones_noca_lora.pt", True)]
 

@@ -140,6 +140,18 @@ def test_attention_simt(dtype, D):
     assert rel_l2(out, ref) < tol
 
 
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("n,BT,K,C,Ct", [(82, 10, 6, 1152, 1152), (41, 10, 3, 1152, 1), (3, 1, 6, 384, 384), (2, 7, 3, 96, 1)])
+def test_adaln_tables_bit_exact(dtype, n, BT, K, C, Ct):
+    """The modulation tables of all blocks in one launch: bit-identical to the reference's add in the model dtype."""
+    tables = rnd(n, K, C, dtype=dtype, seed=n)
+    tsel = rnd(BT, K, Ct, dtype=dtype, seed=BT + K)
+    got = ops().adaln_tables(tables, tsel)
+    want = spec_ops.adaln_tables(tables, tsel)
+    assert got.dtype == torch.float32 and got.shape == (n, BT, K, C)
+    assert torch.equal(got, want)
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("T,D", [(1, 64), (3, 64), (5, 72), (17, 72)])
 def test_temporal_attention(dtype, T, D):
