@@ -494,6 +494,12 @@ def main():
             torch.distributed.destroy_process_group()
         return
 
+    if world > 1:
+        from magicdrive_v2_b200 import sp as _sp
+        cfg["sp_exchange"] = _sp.exchange_path()        # which exchange the sequence-parallel attention took
+        cfg["sp_parity_note"] = ("sp_parity_rel_l2 = || SP output - single-GPU output of the same inputs and weights || / "
+                                 "|| . || on rank 0; 0.0 means bit-identical (every kernel is row- or head-local with a "
+                                 "fixed reduction order, so re-sharding does not change a single bit)")
     ktab = kernel_table(res["kernels"], pk)
     dom = next(iter(ktab))
     drow = ktab[dom]

@@ -73,3 +73,47 @@ def test_sequence_parallel_nccl_world2(wl_name, xm, mode):
         assert (ret[(r, "fused_out_bf16")] > 0) == (mode == "peer_fused"), "wrong output scatter path taken"
         assert ret[(r, "fp32")] < 1e-4, ret[(r, "fp32")]
         assert ret[(r, "bf16")] < 1e-2, ret[(r, "bf16")]
+
+
+def _worker_brush(rank, world, port, fixture, skip_ca, sde, ret):
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for p in (root, os.path.join(root, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    from helpers import brushnet_inputs, build_brushnet, load_golden, rel_l2, sde_inputs
+    from magicdrive_v2_b200 import sp, synth
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    os.environ.pop("MDV2_SP_NCCL", None)
+    os.environ["MDV2_SP_FUSED"] = "1"
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        fix = load_golden(fixture)
+        sp.set_sequence_parallel_group(dist.group.WORLD)
+        for dtype, key in ((torch.float32, "fp32"), (torch.bfloat16, "bf16")):
+            model, wl, kw = build_brushnet(fix["workload"], skip_ca, sde=sde, enable_sequence_parallelism=True)
+            model = model.to(dev, dtype)
+            inp = synth.to_device((sde_inputs if sde else brushnet_inputs)(wl, kw, fix), dev)
+            out = model(**inp)
+            torch.cuda.synchronize()
+            ret[(rank, key)] = rel_l2(out.cpu(), fix["out"])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("fixture,skip_ca,sde", [("brushnet_tiny_9f_None_ca.pt", False, False),
+                                                 ("sde_tiny_9f_first0_noca.pt", True, True)])
+def test_brushnet_sequence_parallel_nccl_world2(fixture, skip_ca, sde):
+    """The third (BrushNet / SDE-BrushNet) stream under sequence parallelism on two GPUs, through libmdv2 and the
+    NVLink peer exchange, against the single-process golden of the REAL reference (magicdrive_stdit3.py:1314-2470)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    world = 2
+    ret = mp.Manager().dict()
+    mp.spawn(_worker_brush, args=(world, _free_port(), fixture, skip_ca, sde, ret), nprocs=world, join=True)
+    for r in range(world):
+        assert ret[(r, "fp32")] < 1e-4, ret[(r, "fp32")]
+        assert ret[(r, "bf16")] < 1e-2, ret[(r, "bf16")]
