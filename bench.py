@@ -509,8 +509,8 @@ def main():
                                                 if drow["bound"] == "tensor" else ", copy bandwidth"),
                     how="CUDA-event pair around every libmdv2 call of one instrumented step, summed per kernel")
     # DRAM traffic of one representative launch per kernel family, from the committed `ncu --set full` captures
-    # (dram__bytes_read.sum + dram__bytes_write.sum; profiles/ncu_traffic_r01.json names launch and capture file)
-    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic_r01.json")
+    # (dram__bytes_read.sum + dram__bytes_write.sum; profiles/ncu_traffic_r02.json names launch and capture file)
+    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic_r02.json")
     # the captures are of the single-GPU 848x1600 launches: other workloads / rank counts run other launch shapes
     if os.path.exists(tpath) and world == 1 and args.workload == "xl_17f_848x1600":
         with open(tpath) as f:

@@ -11,6 +11,7 @@
 // stores).  Two TMEM accumulator stages let the epilogue of tile i overlap the main loop of tile i+1.
 #include <cstdlib>
 #include <mutex>
+#include <string>
 #include <unordered_map>
 
 #include "gemm_epilogue.cuh"
@@ -478,6 +479,10 @@ int launch_mc(const CUtensorMap& ta, const CUtensorMap& tw, const Params& p, cud
     return MDV2_ECUDA;
   }
   MDV2_CHECK_LAUNCH("gemm_sm100");
+  // one name per tile flavour: bench.py lists every instantiation as its own kernel (they are: the launch list shows
+  // three gemm_sm100_kernel<BN, HD> entries), so that the dominant KERNEL of the step is named, not a family
+  static const std::string flavour = "gemm_sm100<" + std::to_string(BN) + "," + std::to_string(HD) + ">";
+  mdv2_note_kernel(flavour.c_str());
   return MDV2_OK;
 }
 
