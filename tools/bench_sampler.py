@@ -33,7 +33,7 @@ class SyntheticTextEncoder:
         return self.model.y_embedder.y_embedding[None].repeat(n, 1, 1)[:, None]
 
 
-def build(args, dev="cuda:0", dtype=torch.bfloat16, on_device=True):
+def build(args, dev="cuda:0", dtype=torch.bfloat16, on_device=True, sp=False):
     """-> (sampler, denoiser, text encoder, z, inpaint inputs, doubled conditions, workload) the way
     scripts/inference_magicdrive.py assembles them before ``scheduler.sample``."""
     from magicdrive_v2_b200 import brushnet, rflow, synth
@@ -41,7 +41,8 @@ def build(args, dev="cuda:0", dtype=torch.bfloat16, on_device=True):
     from magicdrive_v2_b200.inference_utils import add_null_condition
     wl = dict(synth.WORKLOADS["tiny_9f" if args.tiny else "xl_17f_224x400"], b=1, t_pix=args.frames,
               height=args.height, width=args.width)
-    kw = synth.model_kwargs(**dict(wl["model"], force_pad_h_for_sp_size=4))
+    kw = synth.model_kwargs(**dict(wl["model"], force_pad_h_for_sp_size=getattr(args, "pad_sp", 4),
+                                   enable_sequence_parallelism=sp))
     cls = brushnet.MagicDriveSTDiT3SDEBrushNet if args.sde else brushnet.MagicDriveSTDiT3BrushNet
     torch.manual_seed(0)
     with torch.device(dev):
@@ -77,14 +78,26 @@ def parse(argv=None):
     ap.add_argument("--frames", type=int, default=17)
     ap.add_argument("--sde", action="store_true")
     ap.add_argument("--tiny", action="store_true", help="depth-2 / hidden-384 denoiser (plumbing check)")
+    ap.add_argument("--pad-sp", dest="pad_sp", type=int, default=4, help="force_pad_h_for_sp_size of the denoiser")
     return ap.parse_args(argv)
 
 
 def main():
+    """One process per GPU under ``python -m torch.distributed.run`` (sequence parallelism over the ranks, as
+    scripts/inference_magicdrive.py runs the reference on 8 GPUs); a single process otherwise."""
     args = parse()
     from magicdrive_v2_b200 import ops, synth
-    dev = "cuda:0"
-    sched, model, enc, z, pix, cond, wl = build(args, dev)
+    world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", 1), ("RANK", 0), ("LOCAL_RANK", 0)))
+    torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+    sched, model, enc, z, pix, cond, wl = build(args, dev, sp=world > 1)
+    if world > 1:
+        model.sp_group = dist.group.WORLD
     cls = type(model)
 
     def run(steps):
@@ -93,24 +106,34 @@ def main():
                             additional_args=dict(cond), progress=False)
     run(2)                                             # warm-up: workspaces, condition + inpaint caches
     torch.cuda.synchronize()
+    if dist:
+        dist.barrier()
     n0 = ops.launches
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     out = run(args.sampling_steps)
     e1.record()
     torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1)
+    t_ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if dist:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)    # device time, max over the ranks
+    ms = t_ms.item()
     assert torch.isfinite(out).all()
     T = synth.latent_frames(args.frames)
-    print(json.dumps(dict(
-        metric="rectified-flow sampling loop, denoise steps/sec (device-timed)", value=args.sampling_steps / (ms * 1e-3),
-        unit="steps/s", n_gpus=1, sampling_steps=args.sampling_steps, ms_per_step=ms / args.sampling_steps,
-        ms_total=ms, dtype="bf16", data="synthetic", gpu_launches=ops.launches - n0,
-        config=dict(workload=f"{'sde-' if args.sde else ''}brushnet_{args.frames}f_{args.height}x{args.width}",
-                    denoiser=("tiny " if args.tiny else "XL/2 ") + cls.__name__, sampler=type(sched).__name__,
-                    views=6, latent_frames=T, cfg_batch=2,
-                    tokens_per_frame=math.ceil(math.ceil(args.height / 8) / 2) * math.ceil(math.ceil(args.width / 8) / 2),
-                    conditions="encoded once per sample (cache), inpaint encoder once per sample"))))
+    if rank == 0:
+        from magicdrive_v2_b200 import sp as _sp
+        print(json.dumps(dict(
+            metric="rectified-flow sampling loop, denoise steps/sec (device-timed)", value=args.sampling_steps / (ms * 1e-3),
+            unit="steps/s", n_gpus=world, sampling_steps=args.sampling_steps, ms_per_step=ms / args.sampling_steps,
+            ms_total=ms, dtype="bf16", data="synthetic", gpu_launches=ops.launches - n0,
+            config=dict(workload=f"{'sde-' if args.sde else ''}brushnet_{args.frames}f_{args.height}x{args.width}",
+                        denoiser=("tiny " if args.tiny else "XL/2 ") + cls.__name__, sampler=type(sched).__name__,
+                        views=6, latent_frames=T, cfg_batch=2, parallelism=f"sp{world}" if world > 1 else "single",
+                        sp_exchange=_sp.exchange_path() if world > 1 else None,
+                        tokens_per_frame=math.ceil(math.ceil(args.height / 8) / 2) * math.ceil(math.ceil(args.width / 8) / 2),
+                        conditions="encoded once per sample (cache), inpaint encoder once per sample"))), flush=True)
+    if dist:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
