@@ -78,7 +78,7 @@ struct Params {
 template <int BN, int HD, int MC>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-                  const Params p) {
+                  const __grid_constant__ CUtensorMap tmap_wr, const Params p) {
   using C = Cfg<BN, HD>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -96,7 +96,12 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const uint32_t rank = crank & 1;                      // within the pair: 0 = leader (issues the pair's MMAs)
   const uint32_t q = crank >> 1;                        // pair within the cluster: N tile n_super·MC + q
   const int64_t pair = blockIdx.x / (2 * MC), n_pairs = gridDim.x / (2 * MC);      // cluster index / clusters
-  const int n_tiles_n = p.N / BN / MC;                  // cluster tiles along N (MC adjacent BN-wide tiles each)
+  // Column tiles: BN wide, plus — when N is not a multiple of BN — ONE narrower last tile of R = N % BN columns (R a
+  // multiple of 64; MC == 1 only).  N = 1152 runs as 4 x 256 + 128 instead of 6 x 192: the L2 -> SM fabric, not the tensor
+  // pipe, bounds these GEMMs (a CTA pulls (128 + BN/2) x 128 B per k-block: 64 / 75 / 89 B per clock at full tensor rate
+  // for BN = 256 / 192 / 144), so the widest tile wins and the remainder is cheaper as one narrow tile than as 192s.
+  const int R = MC == 1 ? p.N % BN : 0;
+  const int n_tiles_n = p.N / BN / MC + (R ? 1 : 0);    // cluster tiles along N (MC adjacent BN-wide tiles each)
   const int64_t n_tiles_m = (p.M + 2 * BM - 1) / (2 * BM);
   const int64_t n_tiles = n_tiles_m * n_tiles_n;
   const int n_kb = p.K / BK;
@@ -133,11 +138,14 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       uint32_t phase = 0;
       for (int64_t tile = pair; tile < n_tiles; tile += n_pairs) {
         const int m0 = (int)(tile / n_tiles_n) * 2 * BM + (int)rank * BM;
-        const int n0 = ((int)(tile % n_tiles_n) * MC + (int)q) * BN + (int)rank * (BN / 2);
+        const int tn = (int)(tile % n_tiles_n);
+        const bool narrow = R != 0 && tn == n_tiles_n - 1;
+        const int n0 = (tn * MC + (int)q) * BN + (int)rank * ((narrow ? R : BN) / 2);
+        const uint32_t tx = narrow ? 2 * (A_BYTES + (R / 2) * BK * 2) : 2 * C::STAGE_BYTES;
         for (int kb = 0; kb < n_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::STAGE_BYTES;
-          if (rank == 0) mbar_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
+          if (rank == 0) mbar_expect_tx(&full[stage], tx);
           if constexpr (MC == 1) {
             tma_load_2d_pair(sa, &tmap_a, &full[stage], kb * BK, m0);
           } else {
@@ -145,7 +153,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             tma_load_2d_pair_mc(sa + q * (A_BYTES / MC), &tmap_a, &full[stage], kb * BK, m0 + (int)q * (BM / MC),
                                 (uint16_t)(0x5u << rank));
           }
-          tma_load_2d_pair(sa + A_BYTES, &tmap_w, &full[stage], kb * BK, n0);
+          tma_load_2d_pair(sa + A_BYTES, narrow ? &tmap_wr : &tmap_w, &full[stage], kb * BK, n0);
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -153,12 +161,14 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   } else if (warp == 1) {
     // ===== MMA issuer (leader CTA only) =====
     if (lane == 0 && rank == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BN);
+      constexpr uint32_t idesc_full = make_idesc_bf16(2 * BM, BN);
+      const uint32_t idesc_narrow = make_idesc_bf16(2 * BM, R ? R : BN);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int64_t tile = pair; tile < n_tiles; tile += n_pairs) {
+        const uint32_t idesc = (R != 0 && (int)(tile % n_tiles_n) == n_tiles_n - 1) ? idesc_narrow : idesc_full;
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
@@ -200,7 +210,10 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const bool has_res = HD == 0 && ep.res != nullptr, has_gate = HD == 0 && ep.gate_mod != nullptr;
     for (int64_t tile = pair; tile < n_tiles; tile += n_pairs) {
       const int64_t m0 = (tile / n_tiles_n) * 2 * BM + (int64_t)rank * BM;
-      const int n0 = ((int)(tile % n_tiles_n) * MC + (int)q) * BN;
+      const int tn = (int)(tile % n_tiles_n);
+      const int n0 = (tn * MC + (int)q) * BN;
+      // chunks of this warp in the tile: all CPW of them, fewer in the narrow last tile (>= 1: R is a multiple of 2·CW)
+      const int n_ci = (R != 0 && tn == n_tiles_n - 1) ? (R / CW - half + 1) / 2 : CPW;
       const int64_t r0 = m0 + quarter * 32;          // first row of this warp
       {  // per-row epilogue context, once per tile (64-bit divisions stay out of the inner loops)
         const int64_t gr = r0 + lane;
@@ -217,8 +230,9 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
       for (int ci = 0; ci < CPW; ++ci) {
         const int c0 = n0 + (half + 2 * ci) * CW;
-        for (int jj = lane; jj < CW; jj += 32)
-          sbias[ci * CW + jj] = ep.bias ? ep.bias_scale * __bfloat162float(ep.bias[c0 + jj]) : 0.f;
+        if (ci < n_ci)
+          for (int jj = lane; jj < CW; jj += 32)
+            sbias[ci * CW + jj] = ep.bias ? ep.bias_scale * __bfloat162float(ep.bias[c0 + jj]) : 0.f;
       }
       __syncwarp();
       const bool gate_uniform = FIXED_U && has_gate && row_gate[0] == row_gate[31];
@@ -245,7 +259,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       tc_fence_after();
       const uint32_t t_row = tmem_base + acc * ACC_STRIDE + ((uint32_t)(quarter * 32) << 16);
 #pragma unroll 1
-      for (int ci = 0; ci < CPW; ++ci) {
+      for (int ci = 0; ci < n_ci; ++ci) {
         const int ch = half + 2 * ci;
         const int c0 = n0 + ch * CW;
         uint32_t raw[CW];
@@ -257,9 +271,9 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
         for (int it = 0; it < NIT; ++it) cres[it] = rres[it];
         const float4 cg0 = rg0, cg1 = rg1;
-        if (ci + 1 < CPW) prefetch(ci + 1);
+        if (ci + 1 < n_ci) prefetch(ci + 1);
         tmem_ld_wait();
-        if (ci == CPW - 1) {                         // accumulator stage drained: the MMA warp may reuse it
+        if (ci == n_ci - 1) {                        // accumulator stage drained: the MMA warp may reuse it
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive_leader(&tempty[acc]);
@@ -431,7 +445,7 @@ int mdv2_make_tmap_3d_heads(CUtensorMap* out, const void* ptr, uint64_t rows, ui
 
 namespace {
 template <int BN, int HD, int MC>
-int launch_mc(const CUtensorMap& ta, const CUtensorMap& tw, const Params& p, cudaStream_t st) {
+int launch_mc(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& twr, const Params& p, cudaStream_t st) {
   using C = Cfg<BN, HD>;
   auto kern = gemm_sm100_kernel<BN, HD, MC>;
   static PerDeviceFlag configured_flag; bool& configured = configured_flag.here();
@@ -465,7 +479,7 @@ int launch_mc(const CUtensorMap& ta, const CUtensorMap& tw, const Params& p, cud
     max_clusters[dev & 63] = n;
     configured = true;
   }
-  const int64_t tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * (p.N / BN / MC);
+  const int64_t tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * (p.N / BN / MC + ((MC == 1 && p.N % BN) ? 1 : 0));
   int64_t clusters = max_clusters[dev & 63];
   static const int forced_pairs = [] {                 // tuning hook (tools/gemm_pairs_probe.py)
     const char* e = getenv("MDV2_GEMM_PAIRS");
@@ -473,7 +487,7 @@ int launch_mc(const CUtensorMap& ta, const CUtensorMap& tw, const Params& p, cud
   }();
   if (forced_pairs > 0 && forced_pairs / MC < clusters) clusters = forced_pairs / MC > 0 ? forced_pairs / MC : 1;
   cfg.gridDim = dim3((unsigned)(2 * MC * (tiles < clusters ? tiles : clusters)));
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tw, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tw, twr, p);
   if (e != cudaSuccess) {
     mdv2_set_error("gemm_sm100: launch failed: %s", cudaGetErrorString(e));
     return MDV2_ECUDA;
@@ -490,13 +504,14 @@ int launch_mc(const CUtensorMap& ta, const CUtensorMap& tw, const Params& p, cud
 // (profiles/yardstick_gemm_r02.txt): +7 % per SM, but the driver places only 33 such clusters (132 of 148 SMs: GPCs of
 // 18 SMs do not tile by four), so every flavour is 3-5 % slower overall (the qkv flavour 22 %)
 template <int BN, int HD>
-int launch(const CUtensorMap& ta, const CUtensorMap& ta_mc, const CUtensorMap& tw, const Params& p, cudaStream_t st) {
+int launch(const CUtensorMap& ta, const CUtensorMap& ta_mc, const CUtensorMap& tw, const CUtensorMap& twr, const Params& p,
+           cudaStream_t st) {
   static const int mc = [] {
     const char* e = getenv("MDV2_GEMM_MC");
     return e ? atoi(e) : 1;
   }();
-  if (mc == 2 && (p.N / BN) % 2 == 0) return launch_mc<BN, HD, 2>(ta_mc, tw, p, st);
-  return launch_mc<BN, HD, 1>(ta, tw, p, st);
+  if (mc == 2 && p.N % BN == 0 && (p.N / BN) % 2 == 0) return launch_mc<BN, HD, 2>(ta_mc, tw, tw, p, st);
+  return launch_mc<BN, HD, 1>(ta, tw, twr, p, st);
 }
 
 int pick_bn(int N, const RmsArgs* rms) {
@@ -511,6 +526,11 @@ int pick_bn(int N, const RmsArgs* rms) {
   }();
   if ((forced == 256 || forced == 192 || forced == 128 || forced == 64) && N % forced == 0) return forced;
   if (N % 256 == 0) return 256;
+  static const int tail = [] {                         // MDV2_GEMM_TAIL=0: no narrow last tile (N = 1152 as 6 x 192)
+    const char* e = getenv("MDV2_GEMM_TAIL");
+    return e ? atoi(e) : 1;
+  }();
+  if (tail && N > 256 && N % 256 == 128) return 256;   // 256-wide tiles + one 128-wide last tile
   if (N % 192 == 0) return 192;
   if (N % 128 == 0) return 128;
   if (N % 64 == 0) return 64;
@@ -540,6 +560,11 @@ int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void
   if (rc) return rc;
   rc = mdv2_make_tmap_2d(&tw, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)bn / 2, BK);
   if (rc) return rc;
+  CUtensorMap twr = tw;                                  // the narrow last column tile (N % bn columns): its own box height
+  if (N % bn) {
+    rc = mdv2_make_tmap_2d(&twr, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)(N % bn) / 2, BK);
+    if (rc) return rc;
+  }
   Params p;
   p.sc.n_dst = 0;
   if (scatter != nullptr) {
@@ -568,13 +593,13 @@ int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void
   p.n_k = rms ? rms->n_k : 0;
   p.eps = rms ? rms->eps : 0.f;
   switch (bn) {
-    case 256: return launch<256, 0>(ta, ta_mc, tw, p, st);
-    case 192: return launch<192, 0>(ta, ta_mc, tw, p, st);
-    case 64: return launch<64, 0>(ta, ta_mc, tw, p, st);
-    case 144: return launch<144, 72>(ta, ta_mc, tw, p, st);
+    case 256: return launch<256, 0>(ta, ta_mc, tw, twr, p, st);
+    case 192: return launch<192, 0>(ta, ta_mc, tw, twr, p, st);
+    case 64: return launch<64, 0>(ta, ta_mc, tw, twr, p, st);
+    case 144: return launch<144, 72>(ta, ta_mc, tw, twr, p, st);
     case 128:
-      if (rms && rms->wq) return launch<128, 64>(ta, ta_mc, tw, p, st);
-      return launch<128, 0>(ta, ta_mc, tw, p, st);
+      if (rms && rms->wq) return launch<128, 64>(ta, ta_mc, tw, twr, p, st);
+      return launch<128, 0>(ta, ta_mc, tw, twr, p, st);
   }
   MDV2_REQUIRE(false, "gemm_sm100: no tile for N=%d", N);
 }

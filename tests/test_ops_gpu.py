@@ -76,7 +76,7 @@ def test_gemm_simt_epilogues(dtype):
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 128, 64), (128, 256, 128), (300, 192, 256), (1000, 1152, 1152),
-                                   (24000, 1152, 1152), (777, 4608, 1152), (513, 1152, 4608), (200, 64, 1152),
+                                   (24000, 1152, 1152), (777, 4608, 1152), (513, 1152, 4608), (200, 64, 1152), (900, 384, 256), (1300, 640, 1152),
                                    (5000, 384, 64)])
 def test_gemm_tcgen05_plain(M, N, K):
     assert _gemm_case(torch.bfloat16, M, N, K, "tcgen05") < TOL[torch.bfloat16]
