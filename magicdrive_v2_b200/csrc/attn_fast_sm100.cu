@@ -49,6 +49,7 @@ constexpr int TMEM_COLS = 512;    // S_t at 128·t, O_t at 256 + 128·t, Q_t (bf
 constexpr float RETRY_SHIFT = 90.f;             // log2 units added to an overflowed row's reference
 constexpr float L_LIMIT = 1.2089258196146292e24f;   // 2^80
 constexpr int MAX_RETRY = 6;
+constexpr int STAGE_PITCH = 176;  // bytes per staged output row (<= 160 of data; 11 x 16: rows rotate over the bank groups)
 __host__ __device__ constexpr int s_col(int t) { return t * 128; }
 __host__ __device__ constexpr int o_col(int t) { return 256 + t * 128; }
 __host__ __device__ constexpr int q_col(int t) { return 336 + t * 128; }
@@ -426,7 +427,47 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
 #pragma unroll
         for (int u = 0; u < NU; ++u) tmem_ld_x8(o_addr + hf * (DP / 2) + u * 8, r + u * 8);
         tmem_ld_wait();
-        if (q_idx < p.Lq) {
+        // The rows of the LAST set leave through shared memory: a thread owns a row, so its 16-byte stores hit 32
+        // different lines per instruction and the 16 warps of the CTA queue ~2500 single-sector transactions on the
+        // LSU — 2.3 us from "O complete" to CTA exit (profiles/attn_cta_lifeline_r02.txt), all of it outside the K/V
+        // loop.  With every MMA of BOTH tiles done the K/V ring is free: each thread parks its half row there, the
+        // two warps of a row meet, and one bulk copy per row (D·2 contiguous bytes, issued by the row's first warp,
+        // executed by the copy engine) writes it out.
+        const bool staged = set == p.n_sets - 1 && (p.dbg & 16) == 0;
+        if (staged) {
+          if (n_qt == 2) {
+            mbar_wait(&o_full[t ^ 1], (uint32_t)((pass - 1) & 1));
+            tc_fence_after();
+          }
+          uint8_t* srow = smem + (t * BMQ + row) * STAGE_PITCH;
+#pragma unroll
+          for (int u = 0; u < NU; ++u) {
+            const int d = hf * (DP / 2) + u * 8;
+            if (d < p.D) {
+              float f[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(r[u * 8 + i]) * inv;
+              Vec16<bf16> o;
+              o.pack(f);
+              if (set > 0 && q_idx < p.Lq) {
+                Vec16<bf16> pv;
+                pv.raw = prev[u];
+                float gg[8], a[8];
+                pv.unpack(gg);
+                o.unpack(a);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) a[i] += gg[i];
+                o.pack(a);
+              }
+              *reinterpret_cast<uint4*>(srow + d * 2) = o.raw;
+            }
+          }
+          fence_async_smem();                            // generic-proxy writes -> the copy engine's reads
+          named_bar_sync(pair_bar, 64);                  // both halves of the row are in shared memory
+          if (hf == 0 && q_idx < p.Lq) bulk_s2g(frow, srow, (uint32_t)(p.D * 2));
+          bulk_commit();
+          bulk_wait_read0();                             // shared memory must outlive the engine's reads
+        } else if (q_idx < p.Lq) {
 #pragma unroll
           for (int u = 0; u < NU; ++u) {
             const int d = hf * (DP / 2) + u * 8;

@@ -48,7 +48,8 @@ struct PCfg {
   static constexpr int Q_BYTES = NCH * BMQ * 128;
   static constexpr int KV_BYTES = NCH * BNK * 128;
   static constexpr int XCH_FLOATS = 3 * QT * 2 * BMQ;         // reference exchange + two row-sum exchanges
-  static constexpr int SMEM = KV_STAGES * 2 * KV_BYTES + 512 + MASK_WORDS * 4 + XCH_FLOATS * 4 + 1024;
+  static constexpr int STATE_BYTES = 16 * 64;                 // one schedule record per softmax warp
+  static constexpr int SMEM = KV_STAGES * 2 * KV_BYTES + 512 + MASK_WORDS * 4 + XCH_FLOATS * 4 + STATE_BYTES + 1024;
   static_assert(Q_BYTES == KV_BYTES, "a Q tile must fit a K/V stage");
 };
 
@@ -113,10 +114,9 @@ __device__ __forceinline__ void mbar_arrive_a(uint32_t bar) {
 }
 // one half-step: S^hf(tile) -> P.  FIRST / LAST are compile-time so that the steady-state instance carries neither the
 // reference exchange nor the tail mask (nor the registers their operands would occupy through the loop).
-template <int PF, bool FIRST, bool LAST, bool TRACE>
-__device__ __forceinline__ void half_step(uint32_t sh_addr, uint32_t bar_s, uint32_t xm_mine, float c,
-                                          float& moff, uint32_t& par_s, float& l_part, uint32_t cfg, int tail_left,
-                                          uint32_t& slot, uint32_t& slot_prev, int kt, long long* trace) {
+template <int DP, int PF, bool FIRST, bool LAST, bool TRACE>
+__device__ __forceinline__ void half_step(uint32_t sh_addr, uint32_t bar_s, float c, float& moff, uint32_t& par_s,
+                                          float& l_part, uint32_t cfg, int kt, long long* trace) {
   auto mark = [&](int ev) {
     if constexpr (TRACE) {
       if (trace != nullptr && kt < TRACE_STEPS) trace[kt * TRACE_EV + ev] = clk64();
@@ -137,9 +137,13 @@ __device__ __forceinline__ void half_step(uint32_t sh_addr, uint32_t bar_s, uint
       // the LAST half of S(tile kt) is complete, and the tensor pipe completes in issue order: every Q·K^T on this
       // K tile is done, and so is every P·V on the previous V tile whenever a Q·K^T of this tile was issued behind
       // its last half (not so for a one-half last tile: the MMA issuer commits that V tile) — handed back to the
-      // TMA producer under the latency of the load above
+      // TMA producer under the latency of the load above.  (Everything this branch needs is recomputed in it: only
+      // one lane of four warps takes it, and nothing of it may occupy a register through the exponential loop.)
       // k_empty[0] from s_full[t][hf]: the barrier array is k_full[3] k_empty[3] v_full[3] v_empty[3] s_full[4] ...
       const uint32_t bar_ke = bar_s - (4 * KV_STAGES + ((cfg >> 29) & 3u)) * 8 + KV_STAGES * 8;
+      const uint32_t slot0 = (cfg >> 20) & 3u;
+      const uint32_t slot = (slot0 + (uint32_t)kt) % KV_STAGES;                   // ring slot of tile kt
+      const uint32_t slot_prev = FIRST ? (cfg >> 22) & 3u : (slot + KV_STAGES - 1) % KV_STAGES;   // ... of the entry before
       mbar_arrive_a(bar_ke + slot * 8);
       if (!FIRST && (cfg & (1u << 16))) mbar_arrive_a(bar_ke + KE_TO_VE + slot_prev * 8);
       if (FIRST && (cfg & (1u << 18))) {                 // Q is in TMEM (this S tile came from it): its ring entry
@@ -148,7 +152,7 @@ __device__ __forceinline__ void half_step(uint32_t sh_addr, uint32_t bar_s, uint
       }
     }
     tmem_ld_wait();
-    if constexpr (LAST) mask_tail(sr, tail_left - q * CH);
+    if constexpr (LAST) mask_tail(sr, (int)((cfg >> 8) & 0x7fu) - q * CH);       // keys of this half that exist
     if constexpr (FIRST) {
       if (q == 0 && (cfg & (1u << 19))) {
         // the set's reference: max over the first 32 scores of both warps of the row
@@ -160,6 +164,10 @@ __device__ __forceinline__ void half_step(uint32_t sh_addr, uint32_t bar_s, uint
         }
         const float mine = fmaxf(mx0, mx1);
         float other;
+        // own slot of the reference exchange [tile][half][row] (behind the barriers and the redo mask)
+        const uint32_t th = (cfg >> 29) & 3u;
+        const uint32_t xm_mine = bar_s - (4 * KV_STAGES + th) * 8 + 512 + MASK_WORDS * 4 +
+                                 (th * BMQ + (((threadIdx.x >> 5) & 3u) * 32 + (threadIdx.x & 31u))) * 4;
         asm volatile("st.volatile.shared.f32 [%0], %1;" ::"r"(xm_mine), "f"(mine) : "memory");
         named_bar_sync((int)((cfg >> 24) & 15u), 64);
         // the partner warp's slot: key half hf (cfg bit 28) sits BMQ floats before / after
@@ -172,8 +180,6 @@ __device__ __forceinline__ void half_step(uint32_t sh_addr, uint32_t bar_s, uint
     tmem_st_x16(sh_addr + q * (CH / 2), pk);
     if (q == 0) mark(1);
   }
-  slot_prev = slot;
-  slot = slot == KV_STAGES - 1 ? 0 : slot + 1;
   mark(2);
   tmem_st_wait();
   tc_fence_before();
@@ -194,6 +200,7 @@ struct Lay {
   uint64_t *k_full, *k_empty, *v_full, *v_empty, *s_full, *p_full, *o_full, *o_empty, *qt_full, *set_done;
   uint32_t *tmem_slot, *retry_flag, *redo_any, *mma_lock, *redo_mask;
   float *xch_m, *xch_l;
+  uint8_t* state;
   __device__ __forceinline__ explicit Lay(uint8_t* smem) {
     sK = smem;                                          // ring slot s: K (or Q tile 0) at sK + s·KV_BYTES
     sV = sK + KV_STAGES * C::KV_BYTES;                  //              V (or Q tile 1) at sV + s·KV_BYTES
@@ -215,6 +222,7 @@ struct Lay {
     redo_mask = reinterpret_cast<uint32_t*>(s_end + 512);            // bit k: this CTA's k-th item overflowed
     xch_m = reinterpret_cast<float*>(s_end + 512 + MASK_WORDS * 4);  // [tile][half][row]: reference exchange
     xch_l = xch_m + QT * 2 * BMQ;                       // [pass parity][tile][half][row]: row-sum exchange
+    state = reinterpret_cast<uint8_t*>(xch_m + C::XCH_FLOATS);      // [softmax warp]: schedule record (SmState)
   }
 };
 
@@ -236,11 +244,13 @@ __device__ __forceinline__ int next_item(const uint32_t* redo_mask, bool fast, i
   return k;
 }
 
-// The schedule of a softmax warp lives HERE, in a record in local memory that only sm_next() touches — not in registers
-// of the exponential loop: 96 registers per thread is the cap at 19 warps and that loop wants ~75 of them.  (With the
-// schedule inlined around the loop the allocator parked a dozen values in local memory and re-read them every
-// half-step, two of them on every POLL of the S-tile barrier — and local memory shares the L1 / shared-memory port the
-// MMAs read K and V through: 650 instead of 890 TF/s.)
+// The schedule of a softmax warp lives in a record in SHARED memory (one per warp, every lane reads the same words),
+// accessed through volatile pointers — not in registers of the exponential loop: 96 registers per thread is the cap at
+// 19 warps and that loop wants ~75 of them.  (With the schedule in ordinary variables the allocator parked a dozen
+// values in local memory and re-read them every half-step, two of them on every POLL of the S-tile barrier; with the
+// schedule in a local-memory record behind a never-inlined call the steady state was fine but every pass boundary cost
+// ~9000 clk: with 204 KB of shared memory the L1 has ~28 KB left, the 150 KB of stack frames thrash it, and each of the
+// ~100 local loads / stores of the cold path is an L2 round trip — `tools/attn_pers_boundary.py`.)
 struct SmState {
   int started, phase, k, set, attempt, cpass;
   int e6;                      // ring entries so far, mod 6: slot e6 % 3, full-barrier parity e6 / 3
@@ -249,13 +259,14 @@ struct SmState {
   uint32_t par_o;              // parity of the next pass (o_full[t], row-sum exchange buffer)
   int pre;                     // Q_t of the next item is in TMEM already (copied at the end of the previous item)
   int idle;                    // the current item's tile t lies past Lq
+  int npass;                   // (TRACE) passes so far
 };
 
 // End of the pass a softmax warp has just run (row sums, verdict, O, epilogue) and the head of its next one (next set /
 // item / phase, Q_t into TMEM).  Never inlined.  Returns the control word of the next pass.
 template <int DP, bool TRACE>
-__device__ __noinline__ uint32_t sm_next(SmState* st, const AParams* pp, uint8_t* smem, int n_qp, int n_items,
-                                         float l_part, float* moff_io) {
+__device__ __forceinline__ uint32_t sm_next(volatile SmState* st, const AParams* pp, uint8_t* smem, int n_qp, int n_items,
+                                            float l_part, float* moff_io) {
   using C = PCfg<DP>;
   const AParams& p = *pp;
   const Lay<DP> L(smem);
@@ -302,6 +313,19 @@ __device__ __noinline__ uint32_t sm_next(SmState* st, const AParams* pp, uint8_t
     return f == (uint32_t)(cp + 1) && attempt < MAX_RETRY;
   };
 
+  // TRACE builds: where the time between two passes goes (rows 80 + pass of this warp's timeline, lane 0 of CTA 5)
+  long long* btr = nullptr;
+  if constexpr (TRACE) {
+    if (p.trace != nullptr && blockIdx.x == 5 && lane == 0 && st->npass < 12)
+      btr = p.trace + ((int64_t)warp * TRACE_STEPS + 80 + st->npass) * TRACE_EV;
+    st->npass = st->npass + 1;
+  }
+  auto bmark = [&](int ev) {
+    if constexpr (TRACE) {
+      if (btr != nullptr) btr[ev] = clk64();
+    }
+  };
+  bmark(0);
   bool fast = st->phase == 0;
   int k = st->k;
   bool new_item = false;
@@ -309,7 +333,7 @@ __device__ __noinline__ uint32_t sm_next(SmState* st, const AParams* pp, uint8_t
     // ---------------- end of the pass (k, set, attempt) ----------------
     const int set = st->set, attempt = st->attempt;
     const bool idle = st->idle != 0;
-    st->par_h1 ^= (uint32_t)(n_half1 & 1);
+    st->par_h1 = st->par_h1 ^ (uint32_t)(n_half1 & 1);
     st->e6 = add6(st->e6, n_kt);
     const int kn = next_item(L.redo_mask, fast, k, n_my);
     const bool nxt_new = fast && la_on && set + 1 == p.n_sets && kn < n_my;
@@ -319,6 +343,7 @@ __device__ __noinline__ uint32_t sm_next(SmState* st, const AParams* pp, uint8_t
       tc_fence_after();
       copy_q(st->e6, t >= item_at(p, n_qp, kn).n_qt);
     }
+    bmark(1);
     // where this thread's output row lives
     const Item it = item_at(p, n_qp, k);
     const int q_idx = it.q_row0 + t * BMQ + row;
@@ -342,6 +367,7 @@ __device__ __noinline__ uint32_t sm_next(SmState* st, const AParams* pp, uint8_t
       named_bar_sync(pair_bar, 64);
       l_row = l_part + xl[xo];
     }
+    bmark(2);
     const bool ok = l_row < L_LIMIT;                       // false for NaN, too
     bool again = false;
     if (fast) {
@@ -354,11 +380,12 @@ __device__ __noinline__ uint32_t sm_next(SmState* st, const AParams* pp, uint8_t
       __syncwarp();
       if (lane == 0) mbar_arrive(L.set_done);
       again = verdict(st->cpass, attempt);
-      ++st->cpass;
+      st->cpass = st->cpass + 1;
     }
     mbar_wait(&L.o_full[t], st->par_o);                    // every MMA of this tile's pass has completed
-    st->par_o ^= 1;
+    st->par_o = st->par_o ^ 1u;
     tc_fence_after();
+    bmark(3);
     uint32_t r[NU * 8];
     if (!again && !idle) {
 #pragma unroll
@@ -368,6 +395,7 @@ __device__ __noinline__ uint32_t sm_next(SmState* st, const AParams* pp, uint8_t
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(&L.o_empty[t]);             // the next pass may overwrite O_t
+    bmark(4);
     st->pre = nxt_new;
     if (again) {
       if (!ok) *moff_io += RETRY_SHIFT;
@@ -419,6 +447,7 @@ __device__ __noinline__ uint32_t sm_next(SmState* st, const AParams* pp, uint8_t
     k = next_item(L.redo_mask, true, -1, n_my);
     new_item = true;
   }
+  bmark(5);
   // ---------------- head of the next pass ----------------
   if (new_item) {
     while (k >= n_my) {
@@ -438,9 +467,14 @@ __device__ __noinline__ uint32_t sm_next(SmState* st, const AParams* pp, uint8_t
     st->slot_q = slot_of(st->e6);
     st->e6 = add6(st->e6, 1);
   }
+  bmark(6);
   const bool releaser = quarter == 0 && lane == 0;         // lane that hands ring slots back to the producer
   const bool first = st->set == 0 && st->attempt == 0;
-  return (st->idle ? 2u : 0u) | (uint32_t)(releaser && hf == 1) << 16 | (uint32_t)(releaser && hf == 0 && nh_last == 1) << 17 |
+  // keys of this warp's half that exist in the pass's last tile (HB when it never gets there): ctl bits 8-14
+  const int n_mine = hf == 0 ? n_kt : n_half1;
+  const int tail_left = n_mine == n_kt ? p.Lk - (n_kt - 1) * BNK - hf * HB : HB;
+  return (st->idle ? 2u : 0u) | (uint32_t)(tail_left < HB ? (tail_left < 0 ? 0 : tail_left) : HB) << 8 |
+         (uint32_t)(releaser && hf == 1) << 16 | (uint32_t)(releaser && hf == 0 && nh_last == 1) << 17 |
          (uint32_t)first << 18 | (uint32_t)(st->attempt == 0) << 19 | (uint32_t)slot_of(st->e6) << 20 |
          (uint32_t)st->slot_q << 22 | (uint32_t)pair_bar << 24 | (uint32_t)hf << 28 | (uint32_t)(t * 2 + hf) << 29;
 }
@@ -818,37 +852,35 @@ attn_pers_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     const int t = warp >> 3, hf = (warp >> 2) & 1;
     const uint32_t sh_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + s_col(t) + hf * HB;
     const uint32_t bar_s = smem_u32(&s_full[t * 2 + hf]), bar_ke = smem_u32(k_empty);
-    const uint32_t xm_mine = smem_u32(xch_m + (t * 2 + hf) * BMQ + quarter * 32 + lane);
     const float c = p.scale_log2;
     const int n_mine = hf == 0 ? n_kt : n_kt - (nh_last == 1 ? 1 : 0);     // half-steps of this warp per pass
-    // keys of this warp's half that exist in the pass's last tile (HB when it never gets there)
-    const int tail_left = n_mine == n_kt ? p.Lk - (n_kt - 1) * BNK - hf * HB : HB;
     long long* tr = nullptr;
     if constexpr (TRACE) {
       if (tracing && lane == 0) tr = p.trace + (int64_t)warp * TRACE_STEPS * TRACE_EV;
     }
-    SmState st;
-    st.started = 0; st.phase = 0; st.k = 0; st.set = 0; st.attempt = 0; st.cpass = 0; st.e6 = 0; st.slot_q = 0;
-    st.par_h1 = 0; st.par_o = 0; st.pre = 0; st.idle = 0;
+    volatile SmState* const stp = reinterpret_cast<volatile SmState*>(L.state + warp * 64);
+    static_assert(sizeof(SmState) <= 64, "one 64-byte record per warp");
+    stp->started = 0; stp->phase = 0; stp->k = 0; stp->set = 0; stp->attempt = 0; stp->cpass = 0; stp->e6 = 0;
+    stp->slot_q = 0; stp->par_h1 = 0; stp->par_o = 0; stp->pre = 0; stp->idle = 0; stp->npass = 0;
+    __syncwarp();
     float moff = 0.f;                                    // the row's reference, log2 units
     uint32_t par_s = 0;                                  // parity of this warp's next S tile (s_full[t][hf])
-    uint32_t ctl = sm_next<DP, TRACE>(&st, &p, smem, n_qp, n_items, 0.f, &moff);
+    uint32_t ctl = sm_next<DP, TRACE>(stp, &p, smem, n_qp, n_items, 0.f, &moff);
     while (!(ctl & 1u)) {
       float l_part = 0.f;
-      uint32_t slot = (ctl >> 20) & 3u, slot_prev = (ctl >> 22) & 3u;      // slot of tile kt / of the ring entry before it
       if (!(ctl & 2u)) {
         if (n_mine == 1) {
-          half_step<PF, true, true, TRACE>(sh_addr, bar_s, xm_mine, c, moff, par_s, l_part, ctl, tail_left, slot, slot_prev, 0, tr);
+          half_step<DP, PF, true, true, TRACE>(sh_addr, bar_s, c, moff, par_s, l_part, ctl, 0, tr);
         } else if (n_mine > 1) {
-          half_step<PF, true, false, TRACE>(sh_addr, bar_s, xm_mine, c, moff, par_s, l_part, ctl, tail_left, slot, slot_prev, 0, tr);
+          half_step<DP, PF, true, false, TRACE>(sh_addr, bar_s, c, moff, par_s, l_part, ctl, 0, tr);
 #pragma unroll 1
           for (int kt = 1; kt < n_mine - 1; ++kt)
-            half_step<PF, false, false, TRACE>(sh_addr, bar_s, 0u, c, moff, par_s, l_part, ctl, 0, slot, slot_prev, kt, tr);
-          half_step<PF, false, true, TRACE>(sh_addr, bar_s, 0u, c, moff, par_s, l_part, ctl, tail_left, slot, slot_prev,
-                                            n_mine - 1, tr);
+            half_step<DP, PF, false, false, TRACE>(sh_addr, bar_s, c, moff, par_s, l_part, ctl, kt, tr);
+          half_step<DP, PF, false, true, TRACE>(sh_addr, bar_s, c, moff, par_s, l_part, ctl, n_mine - 1, tr);
         }
       } else {
         // a tile past Lq: only the hand-shakes of the pass, so that the ring and the MMA issuer see the same protocol
+        uint32_t slot = (ctl >> 20) & 3u, slot_prev = (ctl >> 22) & 3u;    // slot of tile kt / of the ring entry before it
         for (int kt = 0; kt < n_mine; ++kt) {
           mbar_wait_a(bar_s, par_s);
           par_s ^= 1;
@@ -866,7 +898,7 @@ attn_pers_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           if (lane == 0) mbar_arrive_a(bar_s + 4 * 8);
         }
       }
-      ctl = sm_next<DP, TRACE>(&st, &p, smem, n_qp, n_items, l_part, &moff);
+      ctl = sm_next<DP, TRACE>(stp, &p, smem, n_qp, n_items, l_part, &moff);
     }
   }
   tc_fence_before();
