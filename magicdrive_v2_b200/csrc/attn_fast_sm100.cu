@@ -335,7 +335,8 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       for (int attempt = 0;; ++attempt) {
         float l_part = 0.f;
         for (int kt = 0; kt < n_mine; ++kt, ++cnt) {
-          mbar_wait(&s_full[t * 2 + hf], cnt & 1);
+          if (p.dbg & 32) mbar_wait_parked(&s_full[t * 2 + hf], cnt & 1, 200);   // experiment: parked instead of polling
+          else mbar_wait(&s_full[t * 2 + hf], cnt & 1);
           tc_fence_after();
           mark(cnt, 0);
           if constexpr (TRACE) {
