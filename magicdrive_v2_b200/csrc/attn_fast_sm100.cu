@@ -23,6 +23,12 @@
 //    attention logits (tests: test_attention_tcgen05_rescale_path drives it with logit spreads of hundreds).  With
 //    the maximum gone the inner loop is FFMA2 / MUFU.EX2 / FADD2 / F2FP only, and the O accumulator is never rescaled.
 //  * The last K/V tile's second half is skipped entirely when it holds no keys (Lk mod 128 in 1..64, e.g. 1600).
+//
+// Round-2 note: two epilogue changes were tried on top of this file and REVERTED — the earlier sets' partial sums loaded
+// ahead of the wait for O, and the last set's rows leaving through shared memory + one bulk copy per row (the rows are
+// written with 32 different lines per store instruction).  Both shorten "O complete -> CTA exit" in the life-line trace,
+// but the extra live registers changed the allocation of the whole kernel (96 registers, no slack) and the same-box A/B
+// against this version was 2.7 % slower at S = 5600, 6 % slower with two K/V sets (tools: MDV2_LIB_FILE A/B).
 #include <cstdlib>
 
 #include "attn_common.cuh"
@@ -49,7 +55,6 @@ constexpr int TMEM_COLS = 512;    // S_t at 128·t, O_t at 256 + 128·t, Q_t (bf
 constexpr float RETRY_SHIFT = 90.f;             // log2 units added to an overflowed row's reference
 constexpr float L_LIMIT = 1.2089258196146292e24f;   // 2^80
 constexpr int MAX_RETRY = 6;
-constexpr int STAGE_PITCH = 176;  // bytes per staged output row (<= 160 of data; 11 x 16: rows rotate over the bank groups)
 __host__ __device__ constexpr int s_col(int t) { return t * 128; }
 __host__ __device__ constexpr int o_col(int t) { return 256 + t * 128; }
 __host__ __device__ constexpr int q_col(int t) { return 336 + t * 128; }
@@ -335,8 +340,7 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       for (int attempt = 0;; ++attempt) {
         float l_part = 0.f;
         for (int kt = 0; kt < n_mine; ++kt, ++cnt) {
-          if (p.dbg & 32) mbar_wait_parked(&s_full[t * 2 + hf], cnt & 1, 200);   // experiment: parked instead of polling
-          else mbar_wait(&s_full[t * 2 + hf], cnt & 1);
+          mbar_wait(&s_full[t * 2 + hf], cnt & 1);
           tc_fence_after();
           mark(cnt, 0);
           if constexpr (TRACE) {
@@ -405,70 +409,18 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           continue;
         }
         // normalise, round to bf16, add to what earlier sets left in `out`: this warp takes half of the columns
-        // earlier sets' partial sums of this row: all loads go out NOW and fly under the wait for O.  (They used to sit
-        // behind the stores of the previous unit — same pointer, so the compiler kept load / add / store strictly in
-        // order: five dependent global round trips, 8.5 us from "O complete" to CTA exit instead of 2.3,
-        // profiles/attn_cta_lifeline_r02.txt.)
-        constexpr int NU = DP / 16;                      // 8-column units per warp
-        uint4 prev[NU];
-        if (set > 0 && q_idx < p.Lq) {
-#pragma unroll
-          for (int u = 0; u < NU; ++u) {
-            const int d = hf * (DP / 2) + u * 8;
-            if (d < p.D) prev[u] = *reinterpret_cast<const uint4*>(orow + d);
-          }
-        }
         mbar_wait(&o_full[t], (uint32_t)((pass - 1) & 1));
         tc_fence_after();
         if constexpr (TRACE) {
           if (cta_line && warp == 0 && lane == 0) cta_line[4] = gtime_ns();
         }
         const float inv = 1.f / l_row;
+        constexpr int NU = DP / 16;                      // 8-column units per warp
         uint32_t r[NU * 8];
 #pragma unroll
         for (int u = 0; u < NU; ++u) tmem_ld_x8(o_addr + hf * (DP / 2) + u * 8, r + u * 8);
         tmem_ld_wait();
-        // The rows of the LAST set leave through shared memory: a thread owns a row, so its 16-byte stores hit 32
-        // different lines per instruction and the 16 warps of the CTA queue ~2500 single-sector transactions on the
-        // LSU — 2.3 us from "O complete" to CTA exit (profiles/attn_cta_lifeline_r02.txt), all of it outside the K/V
-        // loop.  With every MMA of BOTH tiles done the K/V ring is free: each thread parks its half row there, the
-        // two warps of a row meet, and one bulk copy per row (D·2 contiguous bytes, issued by the row's first warp,
-        // executed by the copy engine) writes it out.
-        const bool staged = set == p.n_sets - 1 && (p.dbg & 16) == 0;
-        if (staged) {
-          if (n_qt == 2) {
-            mbar_wait(&o_full[t ^ 1], (uint32_t)((pass - 1) & 1));
-            tc_fence_after();
-          }
-          uint8_t* srow = smem + (t * BMQ + row) * STAGE_PITCH;
-#pragma unroll
-          for (int u = 0; u < NU; ++u) {
-            const int d = hf * (DP / 2) + u * 8;
-            if (d < p.D) {
-              float f[8];
-#pragma unroll
-              for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(r[u * 8 + i]) * inv;
-              Vec16<bf16> o;
-              o.pack(f);
-              if (set > 0 && q_idx < p.Lq) {
-                Vec16<bf16> pv;
-                pv.raw = prev[u];
-                float gg[8], a[8];
-                pv.unpack(gg);
-                o.unpack(a);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) a[i] += gg[i];
-                o.pack(a);
-              }
-              *reinterpret_cast<uint4*>(srow + d * 2) = o.raw;
-            }
-          }
-          fence_async_smem();                            // generic-proxy writes -> the copy engine's reads
-          named_bar_sync(pair_bar, 64);                  // both halves of the row are in shared memory
-          if (hf == 0 && q_idx < p.Lq) bulk_s2g(frow, srow, (uint32_t)(p.D * 2));
-          bulk_commit();
-          bulk_wait_read0();                             // shared memory must outlive the engine's reads
-        } else if (q_idx < p.Lq) {
+        if (q_idx < p.Lq) {
 #pragma unroll
           for (int u = 0; u < NU; ++u) {
             const int d = hf * (DP / 2) + u * 8;
@@ -479,10 +431,10 @@ attn_fast_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
               Vec16<bf16> o;
               o.pack(f);
               if (set > 0) {
-                Vec16<bf16> pv;
-                pv.raw = prev[u];
+                Vec16<bf16> prev;
+                prev.raw = *reinterpret_cast<const uint4*>(orow + d);
                 float gg[8], a[8];
-                pv.unpack(gg);
+                prev.unpack(gg);
                 o.unpack(a);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) a[i] += gg[i];
@@ -512,7 +464,7 @@ template <int DP, int PF, bool TRACE>
 int launch_fast(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p, int n_seq,
                 cudaStream_t st) {
   constexpr int SMEM = FCfg<DP>::SMEM;
-  static PerDeviceFlag configured_flag; bool& configured = configured_flag.here();
+  static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(attn_fast_kernel<DP, PF, TRACE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     if (e != cudaSuccess) {

@@ -13,7 +13,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmdv2.so")
+LIB_PATH = os.environ.get("MDV2_LIB_FILE") or os.path.join(_HERE, "libmdv2.so")   # (MDV2_LIB_FILE: A/B builds in tools/)
 
 BACKEND_AUTO, BACKEND_SIMT, BACKEND_TCGEN05 = 0, 1, 2
 _BACKENDS = {None: 0, "auto": 0, "simt": 1, "tcgen05": 2}
