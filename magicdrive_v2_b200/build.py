@@ -7,7 +7,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libmdv2.so")
-SOURCES = ["elementwise.cu", "layout.cu", "sampler.cu", "gemm_simt.cu", "attn_simt.cu", "gemm_sm100.cu", "attn_sm100.cu", "attn_fast_sm100.cu", "attn_pers_sm100.cu", "api.cu", "no_alloc.cu"]
+SOURCES = ["elementwise.cu", "layout.cu", "sampler.cu", "gemm_simt.cu", "attn_simt.cu", "gemm_sm100.cu", "attn_sm100.cu", "attn_fast_sm100.cu", "attn_pers_sm100.cu", "attn_cross_sm100.cu", "api.cu", "no_alloc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

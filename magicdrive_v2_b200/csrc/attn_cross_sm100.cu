@@ -1,0 +1,310 @@
+// attn_cross_sm100.cu — cross-attention onto <= 64 condition tokens (text / box / camera / frame tokens, L ~ 62):
+// MultiHeadCrossAttention of every STDiT3 block (reference blocks.py:678-747, magicdrive_stdit3.py:267-280).
+//
+// The whole K/V of a (sequence, head) is ONE 64-key tile, so a query tile is a single latency chain — load Q, one Q·K^T,
+// one softmax, one P·V, store — with ~62 FLOP per byte: an HBM-bound kernel.  The one-tile-per-CTA flavour of
+// attn_sm100.cu (two CTAs per SM, grid over (query tile, head, sequence)) ran it at 2.1 TB/s, and ncu showed why: 1.94 GB
+// read from DRAM for 0.79 GB of queries.  A head is a 144-byte slice of a 2304-byte row; with the 16 heads of a row
+// block read at sixteen unrelated moments every slice drags its neighbours' sectors in (and every 144-byte output slice
+// its partial sectors) and nothing is left in L2 when the neighbour is finally wanted.  Here ONE CTA per SM walks a
+// contiguous range of items ordered (sequence, query tile, HEAD fastest): the sixteen heads of a 128-row block are read
+// and written back to back by the same SM, so DRAM sees whole rows.
+//   warp 0      TMA producer: per item Q (3-slot ring), K (2 slots) and V (3 slots) — K/V are L2-resident (17 MB)
+//   warp 1      MMA issuer: S_b = Q·K^T (SS, both operands in shared memory), O_b = P_b·V (P from TMEM over S_b);
+//               two TMEM buffers b = item parity, issue order  P·V(i), Q·K^T(i + 2)  so the scores of the next item of
+//               a buffer are under way while its softmax warps still read O.  Two commits per item (S ready, O ready)
+//   warps 2-5   softmax + epilogue of the even items, warps 6-9 of the odd items (thread = query row = TMEM lane):
+//               exact single-tile softmax (row maximum, 2^(s·c − m·c), row sum), P as bf16 pairs over S, then O / l
+//               rounded to bf16, parked in shared memory and written by ONE TMA store per warp (32 rows of one head;
+//               the 4-D output map clips the rows past the end of the sequence).  A bulk copy per ROW (128 copies of
+//               144 B per tile) was tried first: 2.8 us per tile, the copy engine's per-operation cost.
+//               The warps that have seen "S ready" / "O ready" hand the Q + K / the V slot back to the producer with a
+//               plain mbarrier arrive — nothing asynchronous is outstanding when the CTA retires.
+#include <cstdlib>
+
+#include "attn_common.cuh"
+
+using namespace sm100;
+using namespace attn;
+
+namespace {
+constexpr int BNK = 64;           // keys per K/V tile = all of them
+constexpr int Q_SLOTS = 3, K_SLOTS = 2, V_SLOTS = 3;
+constexpr int N_SM_WARPS = 8;     // two groups of four
+constexpr int NTHREADS = (2 + N_SM_WARPS) * 32;
+constexpr int TMEM_COLS = 512;    // S_b (P_b over it) at 128·b, O_b at 256 + 128·b
+__host__ __device__ constexpr int s_col(int b) { return b * 128; }
+__host__ __device__ constexpr int o_col(int b) { return 256 + b * 128; }
+
+template <int DP>
+struct XCfg {
+  static constexpr int NCH = DP > 64 ? 2 : 1;                 // 64-wide d-chunks per row
+  static constexpr int Q_BYTES = NCH * BMQ * 128;
+  static constexpr int KV_BYTES = NCH * BNK * 128;            // one K (or V) tile
+  static constexpr int ROW_BYTES = DP == 64 ? 128 : 144;      // staged output row = D bf16, dense (the TMA box)
+  static constexpr int STAGE_BYTES = 2 * BMQ * ROW_BYTES;     // output rows of the two item parities
+  static constexpr int SMEM = Q_SLOTS * Q_BYTES + (K_SLOTS + V_SLOTS) * KV_BYTES + STAGE_BYTES + 256 + 1024;
+};
+
+template <int DP>
+__global__ void __launch_bounds__(NTHREADS, 1)
+attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
+                  const __grid_constant__ CUtensorMap tv, const __grid_constant__ CUtensorMap to, const AParams p,
+                  const int n_qt, const int n_items) {
+  using C = XCfg<DP>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;                                   // slot s at sQ + s·Q_BYTES
+  uint8_t* sK = sQ + Q_SLOTS * C::Q_BYTES;              // slot s at sK + s·KV_BYTES
+  uint8_t* sV = sK + K_SLOTS * C::KV_BYTES;
+  uint8_t* sO = sV + V_SLOTS * C::KV_BYTES;             // [item parity][row] staged output rows
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sO + C::STAGE_BYTES);
+  uint64_t* q_full = bars;                              // Q_SLOTS
+  uint64_t* q_empty = q_full + Q_SLOTS;
+  uint64_t* k_full = q_empty + Q_SLOTS;                 // K_SLOTS
+  uint64_t* k_empty = k_full + K_SLOTS;
+  uint64_t* v_full = k_empty + K_SLOTS;                 // V_SLOTS
+  uint64_t* v_empty = v_full + V_SLOTS;
+  uint64_t* s_full = v_empty + V_SLOTS;                 // [item parity]
+  uint64_t* p_full = s_full + 2;
+  uint64_t* o_full = p_full + 2;
+  uint64_t* o_free = o_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_free + 2);
+
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+  // this CTA's contiguous range of items; item -> (sequence, query tile, head), head fastest
+  const int64_t G = gridDim.x;
+  const int i0 = (int)((int64_t)n_items * blockIdx.x / G), i1 = (int)((int64_t)n_items * (blockIdx.x + 1) / G);
+  const int n_my = i1 - i0;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tq);
+    prefetch_tmap(&tk);
+    prefetch_tmap(&tv);
+    prefetch_tmap(&to);
+    for (int i = 0; i < Q_SLOTS; ++i) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_empty[i], 1);
+    }
+    for (int i = 0; i < K_SLOTS; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+    }
+    for (int i = 0; i < V_SLOTS; ++i) {
+      mbar_init(&v_full[i], 1);
+      mbar_init(&v_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_full[i], 4);
+      mbar_init(&o_full[i], 1);
+      mbar_init(&o_free[i], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      for (int i = 0; i < n_my; ++i) {
+        const int it = i0 + i, h = it % p.H, r = it / p.H, qt = r % n_qt, seq = r / n_qt;
+        const int ks = i % K_SLOTS, qs = i % Q_SLOTS, vs = i % V_SLOTS;
+        mbar_wait_parked(&k_empty[ks], (uint32_t)(((i / K_SLOTS) & 1) ^ 1), 2000);
+        mbar_expect_tx(&k_full[ks], C::KV_BYTES);
+#pragma unroll
+        for (int c = 0; c < C::NCH; ++c)
+          tma_load_3d(sK + ks * C::KV_BYTES + c * BNK * 128, &tk, &k_full[ks], c * 64, h, seq * p.Lk);
+        mbar_wait_parked(&q_empty[qs], (uint32_t)(((i / Q_SLOTS) & 1) ^ 1), 2000);
+        mbar_expect_tx(&q_full[qs], C::Q_BYTES);
+#pragma unroll
+        for (int c = 0; c < C::NCH; ++c)
+          tma_load_3d(sQ + qs * C::Q_BYTES + c * BMQ * 128, &tq, &q_full[qs], c * 64, h, seq * p.Lq + qt * BMQ);
+        mbar_wait_parked(&v_empty[vs], (uint32_t)(((i / V_SLOTS) & 1) ^ 1), 2000);
+        mbar_expect_tx(&v_full[vs], C::KV_BYTES);
+#pragma unroll
+        for (int c = 0; c < C::NCH; ++c)
+          tma_load_3d(sV + vs * C::KV_BYTES + c * BNK * 128, &tv, &v_full[vs], c * 64, h, seq * p.Lk);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    constexpr uint32_t idesc_qk = make_idesc_bf16(BMQ, BNK, 0, 0);
+    constexpr uint32_t idesc_pv = make_idesc_bf16(BMQ, DP, 0, 1);       // A = P from TMEM, B = V is MN-major
+    const uint64_t dq0 = make_desc_k_sw128(smem_u32(sQ));
+    const uint64_t dk0 = make_desc_k_sw128(smem_u32(sK));
+    const uint64_t dv0 = make_desc_mn_sw128(smem_u32(sV), BNK * 128, 1024);
+    // S_b(i) = Q(i) · K(i)^T
+    auto issue_qk = [&](int i) {
+      const int ks = i % K_SLOTS, qs = i % Q_SLOTS, b = i & 1;
+      mbar_wait_parked(&k_full[ks], (uint32_t)((i / K_SLOTS) & 1), 1000);
+      mbar_wait_parked(&q_full[qs], (uint32_t)((i / Q_SLOTS) & 1), 1000);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t da = dq0 + (uint64_t)(qs * (C::Q_BYTES >> 4));
+        const uint64_t db = dk0 + (uint64_t)(ks * (C::KV_BYTES >> 4));
+#pragma unroll
+        for (int kk = 0; kk < DP / 16; ++kk) {
+          const uint64_t oa = (uint64_t)((kk / 4) * ((BMQ * 128) >> 4) + (kk % 4) * 2);
+          const uint64_t ob = (uint64_t)((kk / 4) * ((BNK * 128) >> 4) + (kk % 4) * 2);
+          umma_bf16_ss(tmem_base + s_col(b), da + oa, db + ob, idesc_qk, kk != 0);
+        }
+        umma_commit(&s_full[b]);                         // also tells the softmax warps that Q and K have been read
+      }
+      __syncwarp();
+    };
+    if (n_my > 0) issue_qk(0);
+    if (n_my > 1) issue_qk(1);
+    for (int i = 0; i < n_my; ++i) {
+      const int b = i & 1, vs = i % V_SLOTS;
+      mbar_wait_parked(&v_full[vs], (uint32_t)((i / V_SLOTS) & 1), 1000);
+      if (i >= 2) mbar_wait_parked(&o_free[b], (uint32_t)(((i >> 1) - 1) & 1), 1000);   // O_b of item i - 2 has been read
+      mbar_wait_parked(&p_full[b], (uint32_t)((i >> 1) & 1), 1000);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t dv = dv0 + (uint64_t)(vs * (C::KV_BYTES >> 4));
+#pragma unroll
+        for (int kk = 0; kk < BNK / 16; ++kk)
+          umma_bf16_ts(tmem_base + o_col(b), tmem_base + s_col(b) + kk * 8, dv + (uint64_t)((kk * 16) * 128 >> 4), idesc_pv,
+                       kk != 0);
+        umma_commit(&o_full[b]);                         // also: V has been read
+      }
+      __syncwarp();
+      if (i + 2 < n_my) issue_qk(i + 2);                 // over the P this P·V has just consumed (in-order pipe)
+    }
+  } else {
+    // ================= softmax + epilogue: group b = (warp - 2) / 4 takes the items of parity b =================
+    const int b = (warp - 2) >> 2;
+    const int quarter = warp & 3;                        // TMEM lane quarter this warp may touch
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    const uint32_t s_addr = lane_addr + s_col(b), o_addr = lane_addr + o_col(b);
+    uint8_t* swarp = sO + (b * BMQ + quarter * 32) * C::ROW_BYTES;   // this warp's 32 staged rows: one TMA box
+    uint8_t* srow = swarp + lane * C::ROW_BYTES;
+    const float c = p.scale_log2;
+    for (int i = b; i < n_my; i += 2) {
+      const int it = i0 + i, h = it % p.H, rr = it / p.H, qt = rr % n_qt, seq = rr / n_qt;
+      const uint32_t ph = (uint32_t)((i >> 1) & 1);
+      mbar_wait(&s_full[b], ph);
+      tc_fence_after();
+      if (quarter == 0 && lane == 0) {                   // Q·K^T has completed: its operands go back to the producer
+        mbar_arrive(&q_empty[i % Q_SLOTS]);
+        mbar_arrive(&k_empty[i % K_SLOTS]);
+      }
+      uint32_t sr[BNK];
+      tmem_ld_x32(s_addr, sr);
+      tmem_ld_x32(s_addr + 32, sr + 32);
+      tmem_ld_wait();
+      // keys past Lk do not exist
+#pragma unroll
+      for (int j = 0; j < BNK; ++j)
+        if (j >= p.Lk) sr[j] = 0xff800000u;
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+      for (int j = 0; j < BNK; j += 4) {
+        mx0 = fmax3(mx0, __uint_as_float(sr[j]), __uint_as_float(sr[j + 1]));
+        mx1 = fmax3(mx1, __uint_as_float(sr[j + 2]), __uint_as_float(sr[j + 3]));
+      }
+      const float moff = fmaxf(mx0, mx1) * c;
+      const float2 c2 = make_float2(c, c), nm2 = make_float2(-moff, -moff);
+      float2 la = make_float2(0.f, 0.f), lb = make_float2(0.f, 0.f);
+      uint32_t pk[BNK / 2];
+#pragma unroll
+      for (int j = 0; j < BNK; j += 4) {
+        const float2 x01 = ffma2(make_float2(__uint_as_float(sr[j]), __uint_as_float(sr[j + 1])), c2, nm2);
+        const float2 x23 = ffma2(make_float2(__uint_as_float(sr[j + 2]), __uint_as_float(sr[j + 3])), c2, nm2);
+        const float2 e01 = make_float2(ex2(x01.x), ex2(x01.y)), e23 = make_float2(ex2(x23.x), ex2(x23.y));
+        la = fadd2(la, e01);
+        lb = fadd2(lb, e23);
+        __nv_bfloat162 b01 = __floats2bfloat162_rn(e01.x, e01.y), b23 = __floats2bfloat162_rn(e23.x, e23.y);
+        pk[j / 2] = *reinterpret_cast<uint32_t*>(&b01);
+        pk[j / 2 + 1] = *reinterpret_cast<uint32_t*>(&b23);
+      }
+      const float l_row = (la.x + la.y) + (lb.x + lb.y);
+      tmem_st_x32(s_addr, pk);
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[b]);
+      // ---- O = P·V back, normalised, through shared memory, one TMA store per warp ----
+      if (lane == 0) bulk_wait_read0();                  // the warp's previous store (two items ago) has left shared memory
+      __syncwarp();
+      mbar_wait(&o_full[b], ph);
+      tc_fence_after();
+      if (quarter == 0 && lane == 0) mbar_arrive(&v_empty[i % V_SLOTS]);   // P·V has completed: V goes back
+      uint32_t r[DP];
+      tmem_ld_x32(o_addr, r);
+      tmem_ld_x32(o_addr + 32, r + 32);
+      if constexpr (DP > 64) tmem_ld_x16(o_addr + 64, r + 64);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&o_free[b]);
+      const float inv = 1.f / l_row;
+#pragma unroll
+      for (int u = 0; u < C::ROW_BYTES / 16; ++u) {
+        float f[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[u * 8 + e]) * inv;
+        Vec16<bf16> o;
+        o.pack(f);
+        // D = 64: 128-byte rows, SW128 like the store map; D = 72: 144-byte rows already rotate over the bank groups
+        const int uu = DP == 64 ? (u ^ (lane & 7)) : u;
+        *reinterpret_cast<uint4*>(srow + uu * 16) = o.raw;
+      }
+      fence_async_smem();                                // generic-proxy writes -> the copy engine
+      __syncwarp();
+      if (lane == 0) {
+        const int r0 = qt * BMQ + quarter * 32;
+        if (r0 < p.Lq) tma_store_4d(&to, swarp, 0, h, r0, seq);
+        bulk_commit();
+      }
+    }
+    if (lane == 0) bulk_wait_read0();                    // shared memory must outlive the engine's reads
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+template <int DP>
+int launch_cross(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p, int n_seq,
+                 cudaStream_t st) {
+  CUtensorMap to;
+  int rc = mdv2_make_tmap_4d_store(&to, p.out, (uint64_t)n_seq, (uint64_t)p.Lq, (uint32_t)p.H, (uint32_t)p.D, (uint64_t)p.ldo, 32);
+  if (rc) return rc;
+  constexpr int SMEM = XCfg<DP>::SMEM;
+  static PerDeviceFlag configured_flag; bool& configured = configured_flag.here();
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(attn_cross_kernel<DP>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    if (e != cudaSuccess) {
+      mdv2_set_error("attention_cross: cannot set %d B dynamic smem: %s", SMEM, cudaGetErrorString(e));
+      return MDV2_ECUDA;
+    }
+    configured = true;
+  }
+  const int n_qt = (p.Lq + BMQ - 1) / BMQ;
+  const int64_t n_items = (int64_t)n_qt * p.H * n_seq;
+  MDV2_REQUIRE(n_items <= 0x7fffffff, "attention_cross: too many work items");
+  int64_t grid = mdv2_num_sms();
+  if (grid > n_items) grid = n_items;
+  attn_cross_kernel<DP><<<(unsigned)grid, NTHREADS, SMEM, st>>>(tq, tk, tv, to, p, n_qt, (int)n_items);
+  MDV2_CHECK_LAUNCH("attention_cross");
+  return MDV2_OK;
+}
+}  // namespace
+
+// called by mdv2_attention_sm100 (attn_sm100.cu) for Lk <= 64, one K/V set, no output scatter (MDV2_ATTN_CROSS=0: the
+// one-tile-per-CTA flavour of attn_sm100.cu)
+int mdv2_attention_cross_launch(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p,
+                                int n_seq, int D, cudaStream_t st) {
+  if (D == 72) return launch_cross<80>(tq, tk, tv, p, n_seq, st);
+  return launch_cross<64>(tq, tk, tv, p, n_seq, st);
+}

@@ -443,6 +443,32 @@ int mdv2_make_tmap_3d_heads(CUtensorMap* out, const void* ptr, uint64_t rows, ui
   return MDV2_OK;
 }
 
+// 4-D bf16 view (d, head, row in sequence, sequence) of a row-major [n_seq·L, ld] activation, for TMA STORES of
+// box_rows output rows of one head: rows past the end of a sequence are clipped by the TMA unit.  No swizzle unless the
+// head is exactly 128 bytes wide (D = 64), where the staged rows are SW128 so that row-per-thread writes spread over
+// the banks.
+int mdv2_make_tmap_4d_store(CUtensorMap* out, void* ptr, uint64_t n_seq, uint64_t L, uint32_t H, uint32_t D, uint64_t ld,
+                            uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    mdv2_set_error("cuTensorMapEncodeTiled unavailable");
+    return MDV2_ECUDA;
+  }
+  cuuint64_t dims[4] = {D, H, L, n_seq};
+  cuuint64_t strides[3] = {(cuuint64_t)D * 2, ld * 2, L * ld * 2};
+  cuuint32_t box[4] = {D, 1, box_rows, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   D == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    mdv2_set_error("cuTensorMapEncodeTiled(4d store) failed (%d) ptr=%p n_seq=%llu L=%llu H=%u D=%u ld=%llu", (int)r, ptr,
+                   (unsigned long long)n_seq, (unsigned long long)L, H, D, (unsigned long long)ld);
+    return MDV2_ECUDA;
+  }
+  return MDV2_OK;
+}
+
 namespace {
 template <int BN, int HD, int MC>
 int launch_mc(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& twr, const Params& p, cudaStream_t st) {

@@ -469,6 +469,58 @@ __device__ __forceinline__ void temporal_head_mma(uint8_t* rows, int pitch, int 
   }
 }
 
+// Scores + softmax of ONE (column, head) with T <= 8 frames on the tensor cores: a single m16n8 tile whose rows t_q
+// and columns t_k >= T are padding (their fragment registers are zero / never loaded).  Lane (g, c) = (lane / 4,
+// lane % 4) loads q[g] and k[g] words of a 16-wide k step (rows 20 banks apart: conflict-free) and ends up with
+// S[g][2c], S[g][2c + 1]; the row softmax runs inside the quad.  P[t_q][0 .. 8) goes, as fp32 and rounded to bf16 like
+// the reference (blocks.py:255-268), over the first 32 bytes of the q slice of row t_q — where phase C reads it.
+// Fewer instructions than one thread per (head, t_q) (which unpacks every k vector T times), but a longer dependent
+// chain per warp: measured 16 % slower at T = 5 — opt-in, MDV2_TEMPORAL_MMA=2.
+template <int TN>
+__device__ __forceinline__ void temporal_scores_mma_t8(uint8_t* rows, int pitch, int part_bytes, int D) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, i2 = (lane & 3) * 2;
+  const bool row_ok = g < TN;
+  uint8_t* qrow = rows + (row_ok ? g : 0) * pitch;
+  const uint8_t* krow = qrow + part_bytes;
+  float c[4] = {0.f, 0.f, 0.f, 0.f};
+  int k0 = 0;
+  for (; k0 + 16 <= D; k0 += 16) {
+    const int off = (k0 + i2) * 2;
+    uint32_t a[4] = {0u, 0u, 0u, 0u};
+    uint32_t b0 = 0u, b1 = 0u;
+    if (row_ok) {
+      a[0] = *reinterpret_cast<const uint32_t*>(qrow + off);
+      a[2] = *reinterpret_cast<const uint32_t*>(qrow + off + 16);
+      b0 = *reinterpret_cast<const uint32_t*>(krow + off);
+      b1 = *reinterpret_cast<const uint32_t*>(krow + off + 16);
+    }
+    mma_bf16_k16(c, a, b0, b1);
+  }
+  if (k0 < D) {                                         // D = 16 m + 8: one k8 step for the tail
+    const int off = (k0 + i2) * 2;
+    uint32_t a0 = 0u, b0 = 0u;
+    if (row_ok) {
+      a0 = *reinterpret_cast<const uint32_t*>(qrow + off);
+      b0 = *reinterpret_cast<const uint32_t*>(krow + off);
+    }
+    mma_bf16_k8(c, a0, 0u, b0);
+  }
+  float v0 = i2 < TN ? round_bf16(c[0]) : -INFINITY;    // q @ k^T leaves the GEMM in bf16
+  float v1 = i2 + 1 < TN ? round_bf16(c[1]) : -INFINITY;
+  float mx = fmaxf(v0, v1);
+  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+  v0 = __expf(v0 - mx);                                 // padding keys: exp(-inf) = 0
+  v1 = __expf(v1 - mx);
+  float den = v0 + v1;
+  den += __shfl_xor_sync(0xffffffffu, den, 1);
+  den += __shfl_xor_sync(0xffffffffu, den, 2);
+  const float inv = 1.f / den;
+  __syncwarp();                                         // every lane's q words are in registers / consumed
+  if (row_ok && (TN > 4 || i2 < 4))
+    *reinterpret_cast<float2*>(qrow + i2 * 4) = make_float2(round_bf16(v0 * inv), round_bf16(v1 * inv));
+}
+
 // ------------------------------------------------------------------------------------------------
 // bf16 production path (T <= 8, D % 8 == 0): shared-memory staged temporal attention.
 // A CTA owns TA_G token columns (β, s).  The T rows q|k|v of a column (3C contiguous bf16 each) arrive by
@@ -518,44 +570,61 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_kernel(const
   const int vpr = C / 8;                                // 16-byte vectors per q (or k, v) row part
   const int vph = D / 8;                                // ... per head
   // ---- A: RoPE on q and k ----
-  for (int i = tid; i < ng * TN * 2 * vpr; i += TA_THREADS) {
-    const int v = i % vpr, part = (i / vpr) & 1, t = (i / (2 * vpr)) % TN, g = i / (2 * vpr * TN);
-    const int d0 = (v % vph) * 8;
-    uint4* ptr = reinterpret_cast<uint4*>(ta_smem + (g * TN + t) * pitch + part * C * 2 + v * 16);
-    Vec16<bf16> x;
-    x.raw = *ptr;
-    float f[8], o[8];
-    x.unpack(f);
-    const float4 c0 = *reinterpret_cast<const float4*>(cos_t + t * D + d0);
-    const float4 c1 = *reinterpret_cast<const float4*>(cos_t + t * D + d0 + 4);
-    const float4 s0 = *reinterpret_cast<const float4*>(sin_t + t * D + d0);
-    const float4 s1 = *reinterpret_cast<const float4*>(sin_t + t * D + d0 + 4);
-    const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
-    const float sn[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+  // A thread keeps ONE 16-byte vector position of the q|k part of a row (byte offset u·16) and walks the frames and
+  // columns: the head-dimension offset is divided out once per thread and the cos / sin vectors are loaded once per
+  // frame.  (One flat index over (column, frame, part, vector) cost 181 instructions per vector, 59 % of the kernel's
+  // instructions, most of them the four runtime divisions and the angle loads.)
+  for (int u = tid; u < 2 * vpr; u += TA_THREADS) {
+    const bool is_q = u < vpr;
+    const int d0 = ((is_q ? u : u - vpr) % vph) * 8;
 #pragma unroll
-    for (int e = 0; e < 8; e += 2) {
-      o[e] = f[e] * cs[e] - f[e + 1] * sn[e];
-      o[e + 1] = f[e + 1] * cs[e + 1] + f[e] * sn[e + 1];
-    }
-    x.pack(o);
-    if (part == 0) {                                    // q = (rope(q) in bf16) * scale, in bf16
-      x.unpack(f);
+    for (int t = 0; t < TN; ++t) {
+      const float4 c0 = *reinterpret_cast<const float4*>(cos_t + t * D + d0);
+      const float4 c1 = *reinterpret_cast<const float4*>(cos_t + t * D + d0 + 4);
+      const float4 s0 = *reinterpret_cast<const float4*>(sin_t + t * D + d0);
+      const float4 s1 = *reinterpret_cast<const float4*>(sin_t + t * D + d0 + 4);
+      const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+      const float sn[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
 #pragma unroll
-      for (int e = 0; e < 8; ++e) f[e] *= scale;
-      x.pack(f);
+      for (int g = 0; g < TA_G; ++g) {
+        if (g < ng) {
+          uint4* ptr = reinterpret_cast<uint4*>(ta_smem + (g * TN + t) * pitch + u * 16);
+          Vec16<bf16> x;
+          x.raw = *ptr;
+          float f[8], o[8];
+          x.unpack(f);
+#pragma unroll
+          for (int e = 0; e < 8; e += 2) {
+            o[e] = f[e] * cs[e] - f[e + 1] * sn[e];
+            o[e + 1] = f[e + 1] * cs[e + 1] + f[e] * sn[e + 1];
+          }
+          x.pack(o);
+          if (is_q) {                                   // q = (rope(q) in bf16) * scale, in bf16
+            x.unpack(f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] *= scale;
+            x.pack(f);
+          }
+          *ptr = x.raw;
+        }
+      }
     }
-    *ptr = x.raw;
   }
   __syncthreads();
-  if (use_mma) {
+  if (use_mma == 1) {
     // ---- B + C on the tensor cores (mma.sync tiles, one warp per (column, head); see temporal_head_mma) ----
     for (int idx = tid >> 5; idx < ng * H; idx += TA_THREADS / 32) {
       const int h = idx % H, g = idx / H;
       temporal_head_mma(ta_smem + g * TN * pitch + h * D * 2, pitch, C * 2, TN, D);
     }
   } else {
-  // ---- B: scores + softmax; P[t_q][0..TN) -> first bytes of this thread's q slice ----
-  if (tid < ng * H * TN) {
+  // ---- B: scores + softmax; P[t_q][0..TN) -> first bytes of the q slice of row t_q ----
+  if (use_mma == 2) {                                   // one warp per (column, head): one m16n8 tile (opt-in)
+    for (int idx = tid >> 5; idx < ng * H; idx += TA_THREADS / 32) {
+      const int h = idx % H, g = idx / H;
+      temporal_scores_mma_t8<TN>(ta_smem + g * TN * pitch + h * D * 2, pitch, C * 2, D);
+    }
+  } else if (tid < ng * H * TN) {                       // default: one thread per (column, head, t_q)
     const int tq = tid % TN, h = (tid / TN) % H, g = tid / (TN * H);
     const uint8_t* qs = ta_smem + (g * TN + tq) * pitch + h * D * 2;
     float acc[TN];
@@ -828,7 +897,13 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
         TA_G * H * Tn <= TA_THREADS) {
       const int64_t n_cols = (int64_t)B * S;
       const unsigned nb = (unsigned)((n_cols + TA_G - 1) / TA_G);
-      static const int short_mma = getenv("MDV2_TEMPORAL_MMA") != nullptr;       // A/B hook: tensor-core phases B + C
+      // A/B hook: 0 scalar scores (default), 1 tensor-core scores AND P·V (temporal_head_mma), 2 tensor-core scores.
+      // Measured at T = 5, 67 200 columns: 0.874 / 1.202 / 1.016 ms — one warp per head is a chain of five dependent
+      // mma.sync on one accumulator; the scalar phase keeps 160 threads busy instead
+      static const int short_mma = [] {
+        const char* e = getenv("MDV2_TEMPORAL_MMA");
+        return e ? atoi(e) : 0;
+      }();
 #define TS_CASE(TT)                                                                                               \
   case TT: {                                                                                                      \
     static PerDeviceFlag configured_flag; bool& configured = configured_flag.here();                                                                               \

@@ -264,6 +264,20 @@ def test_attention_tcgen05_cross_view_and_cross(D):
     assert _attn_case(6, 350, 150, 4, D, kv="cross") < ATTN_TOL         # two K/V tiles, ragged
 
 
+def test_attention_tcgen05_cross_persistent():
+    """<= 64 condition tokens, one K/V set: the persistent single-tile kernel (attn_cross_sm100.cu).  Each CTA walks a
+    contiguous range of (sequence, head, query tile) items: ranges that start / end inside a (sequence, head), K / V
+    buffer hand-over between groups, groups of a single tile, ragged last query tiles, 1 .. 64 keys, more CTAs than
+    items and many items per CTA."""
+    assert _attn_case(6, 400, 62, 4, 72, kv="cross") < ATTN_TOL         # 96 items over 96 CTAs
+    assert _attn_case(3, 5600, 62, 16, 72, kv="cross") < ATTN_TOL       # 2112 items: ~14 per CTA, groups of 44 tiles
+    assert _attn_case(40, 100, 64, 16, 72, kv="cross") < ATTN_TOL       # 640 groups of ONE ragged tile: K / V every item
+    assert _attn_case(7, 333, 1, 5, 64, kv="cross") < ATTN_TOL          # a single key: softmax == 1, output == V
+    assert _attn_case(2, 128, 33, 1, 64, kv="cross") < ATTN_TOL         # 2 items
+    assert _attn_case(1, 77, 17, 1, 72, kv="cross") < ATTN_TOL          # 1 item
+    assert _attn_case(5, 700, 62, 16, 72, kv="cross", q_gain=20.0) < ATTN_TOL   # peaked rows
+
+
 def test_attention_tcgen05_xl_shape():
     assert _attn_case(12, 1400, 1400, 16, 72) < ATTN_TOL
     assert _attn_case(3, 1600, 1600, 16, 72) < ATTN_TOL            # 12.5 key tiles: the last tile's second half is skipped

@@ -1,0 +1,14 @@
+# persistent cross-attention kernel and the short-clip temporal kernel: parity, then same-box A/B
+set -x
+cd /root/repo
+timeout 900 python -m pytest tests/test_ops_gpu.py -x -q -m gpu -k "attention or temporal" 2>&1 | tail -5 | tee gpurun_out/small_tests.txt
+cat > /tmp/xb.py <<'PY'
+import os, sys, torch
+sys.path.insert(0, "/root/repo")
+from tools.bench_attn import bench, accuracy
+accuracy(L=333, Lk=62)
+for n, lq in ((60, 5600), (204, 1600), (60, 1400), (60, 400)):
+    bench(n, lq, 62, kind="cross", iters=10)
+PY
+for i in 1 2; do for c in 1 0; do echo "== MDV2_ATTN_CROSS=$c"; MDV2_ATTN_CROSS=$c timeout 300 python /tmp/xb.py 2>&1 | tail -5; done; done | tee gpurun_out/cross_ab.txt
+for i in 1 2; do for m in 2 0 1; do echo "== MDV2_TEMPORAL_MMA=$m"; MDV2_TEMPORAL_MMA=$m timeout 300 python tools/bench_elem.py 2>&1 | tail -2; done; done | tee gpurun_out/temporal_ab.txt
