@@ -72,6 +72,8 @@ __device__ __forceinline__ float2 ex2_poly2(float2 x) {
 __host__ __device__ constexpr bool poly_pair(int pair, int PF) { return ((pair % 8) * PF) / 8 != (((pair % 8) + 1) * PF) / 8; }
 }  // namespace attn
 
+int mdv2_make_tmap_3d_heads_sw32(CUtensorMap* out, const void* ptr, uint64_t rows, uint32_t H, uint32_t D, uint64_t ld,
+                                 uint32_t box_rows);
 int mdv2_make_tmap_4d_store(CUtensorMap* out, void* ptr, uint64_t n_seq, uint64_t L, uint32_t H, uint32_t D, uint64_t ld,
                             uint32_t box_rows);
 int mdv2_make_tmap_3d_heads(CUtensorMap* out, const void* ptr, uint64_t rows, uint32_t H, uint32_t D, uint64_t ld,

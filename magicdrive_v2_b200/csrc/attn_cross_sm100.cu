@@ -28,8 +28,21 @@ using namespace sm100;
 using namespace attn;
 
 namespace {
+// suspend-time hints (ns) of the producer's / the issuer's barrier waits; tuning hooks.  0 = plain try_wait spin.
+#ifndef MDV2_XATTN_MMA_HINT
+#define MDV2_XATTN_MMA_HINT 0
+#define MDV2_XATTN_TMA_HINT 200
+#endif
+constexpr uint32_t MMA_HINT = MDV2_XATTN_MMA_HINT, TMA_HINT = MDV2_XATTN_TMA_HINT;
+__device__ __forceinline__ void mbar_wait_hint(uint64_t* bar, uint32_t parity, uint32_t hint_ns) {
+  if (hint_ns == 0) mbar_wait(bar, parity);
+  else mbar_wait_parked(bar, parity, hint_ns);
+}
 constexpr int BNK = 64;           // keys per K/V tile = all of them
-constexpr int Q_SLOTS = 3, K_SLOTS = 2, V_SLOTS = 3;
+// Rings: Q is the only operand that comes from DRAM (K / V of a sequence are 0.3 MB and L2-resident), and at ~1.5 us of
+// loaded DRAM latency an SM needs ~65 KB of reads in flight to draw its share of the bandwidth: Q runs Q_AHEAD items
+// ahead of K.  (With a 3-slot Q ring and one in-order producer stream the issuer spent 31 % of its time waiting for Q.)
+constexpr int Q_SLOTS = 6, K_SLOTS = 3, V_SLOTS = 2, Q_AHEAD = Q_SLOTS - K_SLOTS;
 constexpr int N_SM_WARPS = 8;     // two groups of four
 constexpr int NTHREADS = (2 + N_SM_WARPS) * 32;
 constexpr int TMEM_COLS = 512;    // S_b (P_b over it) at 128·b, O_b at 256 + 128·b
@@ -38,26 +51,32 @@ __host__ __device__ constexpr int o_col(int b) { return 256 + b * 128; }
 
 template <int DP>
 struct XCfg {
-  static constexpr int NCH = DP > 64 ? 2 : 1;                 // 64-wide d-chunks per row
-  static constexpr int Q_BYTES = NCH * BMQ * 128;
-  static constexpr int KV_BYTES = NCH * BNK * 128;            // one K (or V) tile
+  // a head of 72 = one 64-wide d-chunk (128-byte rows, SW128) + a 16-wide tail chunk.  The tail of Q and K (K-major MMA
+  // operands, one k16 step) is a 32-byte-row SW32 slab — 4 KB instead of the 16 KB a zero-filled 64-wide box takes — so
+  // that SIX query tiles fit the ring; V (MN-major, both chunks in one MMA) keeps two SW128 chunks
+  static constexpr bool TAIL = DP > 64;
+  static constexpr int Q_MAIN = BMQ * 128, Q_BYTES = Q_MAIN + (TAIL ? BMQ * 32 : 0);
+  static constexpr int K_MAIN = BNK * 128, K_BYTES = K_MAIN + (TAIL ? BNK * 32 : 0);
+  static constexpr int V_BYTES = (TAIL ? 2 : 1) * BNK * 128;
   static constexpr int ROW_BYTES = DP == 64 ? 128 : 144;      // staged output row = D bf16, dense (the TMA box)
   static constexpr int STAGE_BYTES = 2 * BMQ * ROW_BYTES;     // output rows of the two item parities
-  static constexpr int SMEM = Q_SLOTS * Q_BYTES + (K_SLOTS + V_SLOTS) * KV_BYTES + STAGE_BYTES + 256 + 1024;
+  static constexpr int SMEM = Q_SLOTS * Q_BYTES + K_SLOTS * K_BYTES + V_SLOTS * V_BYTES + STAGE_BYTES + 256 + 1024;
+  static_assert(Q_BYTES % 1024 == 0 && K_BYTES % 1024 == 0 && V_BYTES % 1024 == 0, "slots keep the swizzle alignment");
 };
 
 template <int DP>
 __global__ void __launch_bounds__(NTHREADS, 1)
 attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
-                  const __grid_constant__ CUtensorMap tv, const __grid_constant__ CUtensorMap to, const AParams p,
+                  const __grid_constant__ CUtensorMap tv, const __grid_constant__ CUtensorMap to,
+                  const __grid_constant__ CUtensorMap tq1, const __grid_constant__ CUtensorMap tk1, const AParams p,
                   const int n_qt, const int n_items) {
   using C = XCfg<DP>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;                                   // slot s at sQ + s·Q_BYTES
-  uint8_t* sK = sQ + Q_SLOTS * C::Q_BYTES;              // slot s at sK + s·KV_BYTES
-  uint8_t* sV = sK + K_SLOTS * C::KV_BYTES;
-  uint8_t* sO = sV + V_SLOTS * C::KV_BYTES;             // [item parity][row] staged output rows
+  uint8_t* sK = sQ + Q_SLOTS * C::Q_BYTES;              // slot s at sK + s·K_BYTES
+  uint8_t* sV = sK + K_SLOTS * C::K_BYTES;
+  uint8_t* sO = sV + V_SLOTS * C::V_BYTES;              // [item parity][row] staged output rows
   uint64_t* bars = reinterpret_cast<uint64_t*>(sO + C::STAGE_BYTES);
   uint64_t* q_full = bars;                              // Q_SLOTS
   uint64_t* q_empty = q_full + Q_SLOTS;
@@ -82,6 +101,10 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     prefetch_tmap(&tk);
     prefetch_tmap(&tv);
     prefetch_tmap(&to);
+    if (C::TAIL) {
+      prefetch_tmap(&tq1);
+      prefetch_tmap(&tk1);
+    }
     for (int i = 0; i < Q_SLOTS; ++i) {
       mbar_init(&q_full[i], 1);
       mbar_init(&q_empty[i], 1);
@@ -110,25 +133,58 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
 
   if (warp == 0) {
     // ================= TMA producer =================
+    // step i requests Q(i + Q_AHEAD) and K(i) — both slots come back when Q·K^T(i - K_SLOTS) has completed — and then
+    // V(i - 2), whose slot P·V(i - 4) returns a little later; nothing a DRAM read is queued behind waits for long
     if (lane == 0) {
-      for (int i = 0; i < n_my; ++i) {
-        const int it = i0 + i, h = it % p.H, r = it / p.H, qt = r % n_qt, seq = r / n_qt;
-        const int ks = i % K_SLOTS, qs = i % Q_SLOTS, vs = i % V_SLOTS;
-        mbar_wait_parked(&k_empty[ks], (uint32_t)(((i / K_SLOTS) & 1) ^ 1), 2000);
-        mbar_expect_tx(&k_full[ks], C::KV_BYTES);
+      auto coords = [&](int i, int& h, int& qt, int& seq) {
+        const int it = i0 + i, r = it / p.H;
+        h = it - r * p.H;
+        seq = r / n_qt;
+        qt = r - seq * n_qt;
+      };
+      for (int i = -Q_AHEAD; i < n_my + 2; ++i) {
+        int h, qt, seq;
+        const int jq = i + Q_AHEAD;
+        if (jq < n_my) {
+          coords(jq, h, qt, seq);
+          const int qs = jq % Q_SLOTS;
+          uint8_t* dst = sQ + qs * C::Q_BYTES;
+          mbar_wait_hint(&q_empty[qs], (uint32_t)(((jq / Q_SLOTS) & 1) ^ 1), TMA_HINT);
+          if ((p.dbg & 4) && jq >= Q_SLOTS) {            // timing experiment (bit 2): stale Q
+            mbar_arrive(&q_full[qs]);
+          } else {
+            mbar_expect_tx(&q_full[qs], C::Q_BYTES);
+            tma_load_3d(dst, &tq, &q_full[qs], 0, h, seq * p.Lq + qt * BMQ);
+            if (C::TAIL) tma_load_3d(dst + C::Q_MAIN, &tq1, &q_full[qs], 64, h, seq * p.Lq + qt * BMQ);
+          }
+        }
+        if (i >= 0 && i < n_my) {
+          coords(i, h, qt, seq);
+          const int ks = i % K_SLOTS;
+          uint8_t* dst = sK + ks * C::K_BYTES;
+          mbar_wait_hint(&k_empty[ks], (uint32_t)(((i / K_SLOTS) & 1) ^ 1), TMA_HINT);
+          if ((p.dbg & 1) && i >= K_SLOTS) {             // timing experiment (MDV2_ATTN_DBG bit 0): stale K / V, wrong results
+            mbar_arrive(&k_full[ks]);
+          } else {
+            mbar_expect_tx(&k_full[ks], C::K_BYTES);
+            tma_load_3d(dst, &tk, &k_full[ks], 0, h, seq * p.Lk);
+            if (C::TAIL) tma_load_3d(dst + C::K_MAIN, &tk1, &k_full[ks], 64, h, seq * p.Lk);
+          }
+        }
+        const int jv = i - 2;
+        if (jv >= 0 && jv < n_my) {
+          coords(jv, h, qt, seq);
+          const int vs = jv % V_SLOTS;
+          mbar_wait_hint(&v_empty[vs], (uint32_t)(((jv / V_SLOTS) & 1) ^ 1), TMA_HINT);
+          if ((p.dbg & 1) && jv >= V_SLOTS) {
+            mbar_arrive(&v_full[vs]);
+          } else {
+            mbar_expect_tx(&v_full[vs], C::V_BYTES);
 #pragma unroll
-        for (int c = 0; c < C::NCH; ++c)
-          tma_load_3d(sK + ks * C::KV_BYTES + c * BNK * 128, &tk, &k_full[ks], c * 64, h, seq * p.Lk);
-        mbar_wait_parked(&q_empty[qs], (uint32_t)(((i / Q_SLOTS) & 1) ^ 1), 2000);
-        mbar_expect_tx(&q_full[qs], C::Q_BYTES);
-#pragma unroll
-        for (int c = 0; c < C::NCH; ++c)
-          tma_load_3d(sQ + qs * C::Q_BYTES + c * BMQ * 128, &tq, &q_full[qs], c * 64, h, seq * p.Lq + qt * BMQ);
-        mbar_wait_parked(&v_empty[vs], (uint32_t)(((i / V_SLOTS) & 1) ^ 1), 2000);
-        mbar_expect_tx(&v_full[vs], C::KV_BYTES);
-#pragma unroll
-        for (int c = 0; c < C::NCH; ++c)
-          tma_load_3d(sV + vs * C::KV_BYTES + c * BNK * 128, &tv, &v_full[vs], c * 64, h, seq * p.Lk);
+            for (int c = 0; c < (C::TAIL ? 2 : 1); ++c)
+              tma_load_3d(sV + vs * C::V_BYTES + c * BNK * 128, &tv, &v_full[vs], c * 64, h, seq * p.Lk);
+          }
+        }
       }
     }
     __syncwarp();
@@ -136,24 +192,21 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     // ================= MMA issuer =================
     constexpr uint32_t idesc_qk = make_idesc_bf16(BMQ, BNK, 0, 0);
     constexpr uint32_t idesc_pv = make_idesc_bf16(BMQ, DP, 0, 1);       // A = P from TMEM, B = V is MN-major
-    const uint64_t dq0 = make_desc_k_sw128(smem_u32(sQ));
-    const uint64_t dk0 = make_desc_k_sw128(smem_u32(sK));
+    const uint64_t dq0 = make_desc_k_sw128(smem_u32(sQ)), dq1 = make_desc_k_sw32(smem_u32(sQ + C::Q_MAIN));
+    const uint64_t dk0 = make_desc_k_sw128(smem_u32(sK)), dk1 = make_desc_k_sw32(smem_u32(sK + C::K_MAIN));
     const uint64_t dv0 = make_desc_mn_sw128(smem_u32(sV), BNK * 128, 1024);
     // S_b(i) = Q(i) · K(i)^T
     auto issue_qk = [&](int i) {
       const int ks = i % K_SLOTS, qs = i % Q_SLOTS, b = i & 1;
-      mbar_wait_parked(&k_full[ks], (uint32_t)((i / K_SLOTS) & 1), 1000);
-      mbar_wait_parked(&q_full[qs], (uint32_t)((i / Q_SLOTS) & 1), 1000);
+      mbar_wait_hint(&k_full[ks], (uint32_t)((i / K_SLOTS) & 1), MMA_HINT);
+      mbar_wait_hint(&q_full[qs], (uint32_t)((i / Q_SLOTS) & 1), MMA_HINT);
       tc_fence_after();
       if (elect_one()) {
-        const uint64_t da = dq0 + (uint64_t)(qs * (C::Q_BYTES >> 4));
-        const uint64_t db = dk0 + (uint64_t)(ks * (C::KV_BYTES >> 4));
+        const uint64_t oq = (uint64_t)(qs * (C::Q_BYTES >> 4)), ok = (uint64_t)(ks * (C::K_BYTES >> 4));
 #pragma unroll
-        for (int kk = 0; kk < DP / 16; ++kk) {
-          const uint64_t oa = (uint64_t)((kk / 4) * ((BMQ * 128) >> 4) + (kk % 4) * 2);
-          const uint64_t ob = (uint64_t)((kk / 4) * ((BNK * 128) >> 4) + (kk % 4) * 2);
-          umma_bf16_ss(tmem_base + s_col(b), da + oa, db + ob, idesc_qk, kk != 0);
-        }
+        for (int kk = 0; kk < 4; ++kk)                   // d = 0 .. 63: 32-byte steps inside the SW128 rows
+          umma_bf16_ss(tmem_base + s_col(b), dq0 + oq + (uint64_t)(kk * 2), dk0 + ok + (uint64_t)(kk * 2), idesc_qk, kk != 0);
+        if (C::TAIL) umma_bf16_ss(tmem_base + s_col(b), dq1 + oq, dk1 + ok, idesc_qk, 1);   // d = 64 .. 79 (72 .. 79 are zeros)
         umma_commit(&s_full[b]);                         // also tells the softmax warps that Q and K have been read
       }
       __syncwarp();
@@ -162,12 +215,12 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     if (n_my > 1) issue_qk(1);
     for (int i = 0; i < n_my; ++i) {
       const int b = i & 1, vs = i % V_SLOTS;
-      mbar_wait_parked(&v_full[vs], (uint32_t)((i / V_SLOTS) & 1), 1000);
-      if (i >= 2) mbar_wait_parked(&o_free[b], (uint32_t)(((i >> 1) - 1) & 1), 1000);   // O_b of item i - 2 has been read
-      mbar_wait_parked(&p_full[b], (uint32_t)((i >> 1) & 1), 1000);
+      mbar_wait_hint(&v_full[vs], (uint32_t)((i / V_SLOTS) & 1), MMA_HINT);
+      if (i >= 2) mbar_wait_hint(&o_free[b], (uint32_t)(((i >> 1) - 1) & 1), MMA_HINT);   // O_b of item i - 2 has been read
+      mbar_wait_hint(&p_full[b], (uint32_t)((i >> 1) & 1), MMA_HINT);
       tc_fence_after();
       if (elect_one()) {
-        const uint64_t dv = dv0 + (uint64_t)(vs * (C::KV_BYTES >> 4));
+        const uint64_t dv = dv0 + (uint64_t)(vs * (C::V_BYTES >> 4));
 #pragma unroll
         for (int kk = 0; kk < BNK / 16; ++kk)
           umma_bf16_ts(tmem_base + o_col(b), tmem_base + s_col(b) + kk * 8, dv + (uint64_t)((kk * 16) * 128 >> 4), idesc_pv,
@@ -186,8 +239,16 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     uint8_t* swarp = sO + (b * BMQ + quarter * 32) * C::ROW_BYTES;   // this warp's 32 staged rows: one TMA box
     uint8_t* srow = swarp + lane * C::ROW_BYTES;
     const float c = p.scale_log2;
+    // (sequence, query tile, head) of the warp's current item, stepped by two items per turn: four runtime divisions
+    // per item were 7 % of the kernel's instructions, on the chain between two tiles
+    int h, qt, seq;
+    {
+      const int it = i0 + b, rr = it / p.H;
+      h = it - rr * p.H;
+      seq = rr / n_qt;
+      qt = rr - seq * n_qt;
+    }
     for (int i = b; i < n_my; i += 2) {
-      const int it = i0 + i, h = it % p.H, rr = it / p.H, qt = rr % n_qt, seq = rr / n_qt;
       const uint32_t ph = (uint32_t)((i >> 1) & 1);
       mbar_wait(&s_full[b], ph);
       tc_fence_after();
@@ -200,9 +261,17 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
       tmem_ld_x32(s_addr + 32, sr + 32);
       tmem_ld_wait();
       // keys past Lk do not exist
+      if (p.Lk < BNK) {                                  // (a compare + select per score was 14 % of the instructions)
+        if (p.Lk >= BNK - 8) {
 #pragma unroll
-      for (int j = 0; j < BNK; ++j)
-        if (j >= p.Lk) sr[j] = 0xff800000u;
+          for (int j = BNK - 8; j < BNK; ++j)
+            if (j >= p.Lk) sr[j] = 0xff800000u;
+        } else {
+#pragma unroll
+          for (int j = 0; j < BNK; ++j)
+            if (j >= p.Lk) sr[j] = 0xff800000u;
+        }
+      }
       float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
       for (int j = 0; j < BNK; j += 4) {
@@ -260,8 +329,16 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
       __syncwarp();
       if (lane == 0) {
         const int r0 = qt * BMQ + quarter * 32;
-        if (r0 < p.Lq) tma_store_4d(&to, swarp, 0, h, r0, seq);
+        if (r0 < p.Lq && !(p.dbg & 2)) tma_store_4d(&to, swarp, 0, h, r0, seq);
         bulk_commit();
+      }
+      h += 2;
+      while (h >= p.H) {
+        h -= p.H;
+        if (++qt == n_qt) {
+          qt = 0;
+          ++seq;
+        }
       }
     }
     if (lane == 0) bulk_wait_read0();                    // shared memory must outlive the engine's reads
@@ -276,8 +353,14 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
 
 template <int DP>
 int launch_cross(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p, int n_seq,
-                 cudaStream_t st) {
-  CUtensorMap to;
+                 const void* q, int64_t ldq, const void* k, int64_t ldk, cudaStream_t st) {
+  CUtensorMap to, tq1 = tq, tk1 = tk;
+  if (XCfg<DP>::TAIL) {
+    int rc1 = mdv2_make_tmap_3d_heads_sw32(&tq1, q, (uint64_t)n_seq * p.Lq, (uint32_t)p.H, (uint32_t)p.D, (uint64_t)ldq, BMQ);
+    if (rc1) return rc1;
+    rc1 = mdv2_make_tmap_3d_heads_sw32(&tk1, k, (uint64_t)n_seq * p.Lk, (uint32_t)p.H, (uint32_t)p.D, (uint64_t)ldk, BNK);
+    if (rc1) return rc1;
+  }
   int rc = mdv2_make_tmap_4d_store(&to, p.out, (uint64_t)n_seq, (uint64_t)p.Lq, (uint32_t)p.H, (uint32_t)p.D, (uint64_t)p.ldo, 32);
   if (rc) return rc;
   constexpr int SMEM = XCfg<DP>::SMEM;
@@ -295,7 +378,7 @@ int launch_cross(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap
   MDV2_REQUIRE(n_items <= 0x7fffffff, "attention_cross: too many work items");
   int64_t grid = mdv2_num_sms();
   if (grid > n_items) grid = n_items;
-  attn_cross_kernel<DP><<<(unsigned)grid, NTHREADS, SMEM, st>>>(tq, tk, tv, to, p, n_qt, (int)n_items);
+  attn_cross_kernel<DP><<<(unsigned)grid, NTHREADS, SMEM, st>>>(tq, tk, tv, to, tq1, tk1, p, n_qt, (int)n_items);
   MDV2_CHECK_LAUNCH("attention_cross");
   return MDV2_OK;
 }
@@ -304,7 +387,7 @@ int launch_cross(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap
 // called by mdv2_attention_sm100 (attn_sm100.cu) for Lk <= 64, one K/V set, no output scatter (MDV2_ATTN_CROSS=0: the
 // one-tile-per-CTA flavour of attn_sm100.cu)
 int mdv2_attention_cross_launch(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p,
-                                int n_seq, int D, cudaStream_t st) {
-  if (D == 72) return launch_cross<80>(tq, tk, tv, p, n_seq, st);
-  return launch_cross<64>(tq, tk, tv, p, n_seq, st);
+                                int n_seq, int D, const void* q, int64_t ldq, const void* k, int64_t ldk, cudaStream_t st) {
+  if (D == 72) return launch_cross<80>(tq, tk, tv, p, n_seq, q, ldq, k, ldk, st);
+  return launch_cross<64>(tq, tk, tv, p, n_seq, q, ldq, k, ldk, st);
 }

@@ -498,7 +498,7 @@ int mdv2_attention_fast_launch(const CUtensorMap& tq, const CUtensorMap& tk, con
 int mdv2_attention_pers_launch(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p,
                                int n_seq, int D, bool trace, cudaStream_t st);
 int mdv2_attention_cross_launch(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p,
-                                int n_seq, int D, cudaStream_t st);
+                                int n_seq, int D, const void* q, int64_t ldq, const void* k, int64_t ldk, cudaStream_t st);
 
 bool mdv2_attention_sm100_supported(int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int Lq, int Lk, int H, int D,
                                     int n_sets) {
@@ -569,7 +569,7 @@ int mdv2_attention_sm100(const void* q, int64_t ldq, const void* k, int64_t ldk,
   }();
   // <= 64 keys, one K/V set, rows stay on this rank: the persistent single-tile kernel (attn_cross_sm100.cu)
   if (bnk == 64 && cross && n_sets == 1 && kv_map == nullptr && scatter == nullptr && g_attn_trace == nullptr)
-    return mdv2_attention_cross_launch(tq, tk, tv, p, n_seq, D, st);
+    return mdv2_attention_cross_launch(tq, tk, tv, p, n_seq, D, q, ldq, k, ldk, st);
   if (bnk == 128 && fast && persist) return mdv2_attention_pers_launch(tq, tk, tv, p, n_seq, D, g_attn_trace != nullptr, st);
   if (bnk == 128 && fast) return mdv2_attention_fast_launch(tq, tk, tv, p, n_seq, D, g_attn_trace != nullptr, st);
   if (D == 72 && bnk == 128 && g_attn_trace) {

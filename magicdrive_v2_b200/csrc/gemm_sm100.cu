@@ -29,8 +29,13 @@ constexpr int TMEM_COLS = 512, ACC_STRIDE = 256;
 template <int BN, int HD>
 struct Cfg {
   static constexpr int CW = HD ? HD : 32;                // epilogue chunk width (columns)
-  static constexpr int CPW = BN / CW / 2;                // chunks per epilogue warp and tile (column halves interleave)
-  static constexpr int B_BYTES = (BN / 2) * BK * 2;      // this CTA's half of the W tile
+  // BN = 216 = three heads of 72: 216 is not an MMA width (N % 16 == 0), so the MMA runs 224 wide — each CTA of the pair
+  // fetches 112 W rows, the last 8 of the pair belong to the next tile (or are TMA zero fill) and their accumulator
+  // columns are never read.  3.7 % of wasted tensor work for 20 % less operand traffic per FLOP than two heads per tile.
+  static constexpr int BNM = BN == 216 ? 224 : BN;       // MMA width = W rows fetched per pair and k-block
+  static constexpr int NCH = BN / CW;                    // chunks per tile
+  static constexpr int CPW = (NCH + 1) / 2;              // chunks per epilogue warp and tile (column halves interleave)
+  static constexpr int B_BYTES = (BNM / 2) * BK * 2;     // this CTA's half of the W tile
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int PITCH = ((CW * 2 / 16) % 2 == 1) ? CW * 2 : CW * 2 + 16;   // odd multiple of 16 B
   static constexpr int EPW = 32 * PITCH + 512 + CPW * CW * 4;   // per warp: staging + row info + bias (fp32)
@@ -39,7 +44,7 @@ struct Cfg {
   static constexpr int STAGES_RAW = (232448 - 1024 - 256 - STAGING - RMSW) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
   static constexpr int SMEM = STAGES * STAGE_BYTES + STAGING + RMSW + 256 + 1024;  // + barriers + align slack
-  static_assert(BN % (2 * CW) == 0, "every epilogue warp takes the same number of chunks");
+  static_assert(BN % CW == 0 && BNM <= ACC_STRIDE, "whole chunks, one accumulator stage per tile");
   static_assert(EPW % 16 == 0, "per-warp staging must stay 16-byte aligned");
   static_assert((PITCH / 16) % 2 == 1, "staging pitch must be an odd multiple of 16 B");
   static_assert(B_BYTES % 1024 == 0, "B stage must keep 1024-B alignment");
@@ -83,7 +88,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + C::STAGES * C::STAGE_BYTES;
-  float* s_rms = reinterpret_cast<float*>(staging + C::STAGING);          // [2][HD]: q weights, k weights
+  uint32_t* s_rms = reinterpret_cast<uint32_t*>(staging + C::STAGING);   // [2][HD / 2]: q, k RMSNorm weights as bf16 pairs
   uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::STAGING + C::RMSW);
   uint64_t* full = bars;
   uint64_t* empty = bars + C::STAGES;
@@ -121,9 +126,12 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   }
   if (warp == 1) tmem_alloc_pair(tmem_slot, TMEM_COLS);
   if constexpr (HD != 0) {
-    for (int i = threadIdx.x; i < 2 * HD; i += NUM_THREADS) {
-      const bf16* w = i < HD ? p.rms_q : p.rms_k;
-      s_rms[i] = w ? __bfloat162float(w[i % HD]) : 1.f;
+    for (int i = threadIdx.x; i < HD; i += NUM_THREADS) {                 // pair i % (HD/2) of the q (i < HD/2) or k weights
+      const bf16* w = i < HD / 2 ? p.rms_q : p.rms_k;
+      const int j = (i % (HD / 2)) * 2;
+      const __nv_bfloat162 one = __floats2bfloat162_rn(1.f, 1.f);
+      __nv_bfloat162 v2 = w ? __halves2bfloat162(w[j], w[j + 1]) : one;
+      s_rms[i] = *reinterpret_cast<uint32_t*>(&v2);
     }
   }
   tc_fence_before();
@@ -140,7 +148,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         const int m0 = (int)(tile / n_tiles_n) * 2 * BM + (int)rank * BM;
         const int tn = (int)(tile % n_tiles_n);
         const bool narrow = R != 0 && tn == n_tiles_n - 1;
-        const int n0 = (tn * MC + (int)q) * BN + (int)rank * ((narrow ? R : BN) / 2);
+        const int n0 = (tn * MC + (int)q) * BN + (int)rank * ((narrow ? R : C::BNM) / 2);
         const uint32_t tx = narrow ? 2 * (A_BYTES + (R / 2) * BK * 2) : 2 * C::STAGE_BYTES;
         for (int kb = 0; kb < n_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
@@ -160,8 +168,13 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
   } else if (warp == 1) {
     // ===== MMA issuer (leader CTA only) =====
-    if (lane == 0 && rank == 0) {
-      constexpr uint32_t idesc_full = make_idesc_bf16(2 * BM, BN);
+    // The whole warp walks the loop and ONE ELECTED lane issues the four MMAs + the commit of a k-block.  Under a plain
+    // `lane == 0` branch the compiler cannot keep the descriptors in uniform registers: every UTCHMMA came wrapped in an
+    // election loop with seven register -> uniform-register moves, ~19 instructions per MMA on one lane — longer than a
+    // 256 x 144 x 16 MMA takes to execute, so the two-head qkv tiles were issue-bound (the same finding as in the
+    // attention kernel, attn_sm100.cu).
+    if (rank == 0) {
+      constexpr uint32_t idesc_full = make_idesc_bf16(2 * BM, C::BNM);
       const uint32_t idesc_narrow = make_idesc_bf16(2 * BM, R ? R : BN);
       int stage = 0;
       uint32_t phase = 0;
@@ -175,15 +188,19 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         for (int kb = 0; kb < n_kb; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * C::STAGE_BYTES);
-          const uint64_t da = make_desc_k_sw128(sa), db = make_desc_k_sw128(sa + A_BYTES);
+          if (elect_one()) {
+            const uint32_t sa = smem_u32(smem + stage * C::STAGE_BYTES);
+            const uint64_t da = make_desc_k_sw128(sa), db = make_desc_k_sw128(sa + A_BYTES);
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            umma_bf16_ss_pair(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
-          umma_commit_mc(&empty[stage], (uint16_t)((1u << (2 * MC)) - 1));     // every CTA of the cluster
+            for (int k = 0; k < BK / 16; ++k)
+              umma_bf16_ss_pair(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+            umma_commit_mc(&empty[stage], (uint16_t)((1u << (2 * MC)) - 1));     // every CTA of the cluster
+          }
+          __syncwarp();
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit_mc(&tfull[acc], (uint16_t)(3u << (2 * q)));                 // the two CTAs of this pair
+        if (elect_one()) umma_commit_mc(&tfull[acc], (uint16_t)(3u << (2 * q)));  // the two CTAs of this pair
+        __syncwarp();
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -213,7 +230,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const int tn = (int)(tile % n_tiles_n);
       const int n0 = (tn * MC + (int)q) * BN;
       // chunks of this warp in the tile: all CPW of them, fewer in the narrow last tile (>= 1: R is a multiple of 2·CW)
-      const int n_ci = (R != 0 && tn == n_tiles_n - 1) ? (R / CW - half + 1) / 2 : CPW;
+      const int n_ci = ((R != 0 && tn == n_tiles_n - 1 ? R / CW : C::NCH) - half + 1) / 2;
       const int64_t r0 = m0 + quarter * 32;          // first row of this warp
       {  // per-row epilogue context, once per tile (64-bit divisions stay out of the inner loops)
         const int64_t gr = r0 + lane;
@@ -266,6 +283,92 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         tmem_ld_x32(t_row + ch * CW, raw);
         if constexpr (CW >= 64) tmem_ld_x32(t_row + ch * CW + 32, raw + 32);
         if constexpr (CW == 72) tmem_ld_x8(t_row + ch * CW + 64, raw + 64);
+        if constexpr (HD != 0) {
+          // ---- the qkv flavour: a chunk is one head.  Its own lean path: the general one below kept 18 row addresses
+          // live across the chunk loop and spilled them, and with the shared-memory carve-out at its maximum the L1 that
+          // backs local memory is a few KB — every reload was an L2 round trip, 28 % of the kernel's stall samples,
+          // and the epilogue warps, not the tensor pipe, set the pace of this flavour (ncu, profiles/) ----
+          tmem_ld_wait();
+          if (ci == n_ci - 1) {                        // accumulator stage drained: the MMA warp may reuse it
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(&tempty[acc]);
+          }
+          const float* sb = sbias + ci * CW;
+          float ss = 0.f;
+#pragma unroll
+          for (int jj = 0; jj < CW; jj += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(sb + jj);
+            const float x0 = __uint_as_float(raw[jj + 0]) + b4.x, x1 = __uint_as_float(raw[jj + 1]) + b4.y;
+            const float x2 = __uint_as_float(raw[jj + 2]) + b4.z, x3 = __uint_as_float(raw[jj + 3]) + b4.w;
+            ss += x0 * x0;
+            ss += x1 * x1;
+            ss += x2 * x2;
+            ss += x3 * x3;
+            raw[jj + 0] = __float_as_uint(x0);
+            raw[jj + 1] = __float_as_uint(x1);
+            raw[jj + 2] = __float_as_uint(x2);
+            raw[jj + 3] = __float_as_uint(x3);
+          }
+          const int wsel = c0 < p.n_q ? 0 : (c0 < p.n_q + p.n_k ? 1 : 2);
+          uint8_t* srow = stg + lane * C::PITCH;
+          if (wsel < 2) {
+            // LlamaRMSNorm: weight * (x * rsqrt(mean x^2 + eps)).to(bf16), the product rounded to bf16 once (the exact
+            // product of two bf16 fits fp32, so one HMUL2.BF16 gives what fp32 multiply + round gave)
+            const float r = rsqrtf(ss / CW + p.eps);
+            const uint32_t* w2 = s_rms + wsel * (HD / 2);
+#pragma unroll
+            for (int jj = 0; jj < CW; jj += 8) {
+              const uint4 wv = *reinterpret_cast<const uint4*>(w2 + jj / 2);
+              const uint32_t ww[4] = {wv.x, wv.y, wv.z, wv.w};
+              uint32_t o[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                __nv_bfloat162 hv = __floats2bfloat162_rn(__uint_as_float(raw[jj + 2 * e]) * r,
+                                                          __uint_as_float(raw[jj + 2 * e + 1]) * r);
+                hv = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&ww[e]), hv);
+                o[e] = *reinterpret_cast<uint32_t*>(&hv);
+              }
+              *reinterpret_cast<uint4*>(srow + jj * 2) = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+          } else {
+#pragma unroll
+            for (int jj = 0; jj < CW; jj += 8) {
+              uint32_t o[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                __nv_bfloat162 hv = __floats2bfloat162_rn(__uint_as_float(raw[jj + 2 * e]), __uint_as_float(raw[jj + 2 * e + 1]));
+                o[e] = *reinterpret_cast<uint32_t*>(&hv);
+              }
+              *reinterpret_cast<uint4*>(srow + jj * 2) = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+          }
+          __syncwarp();
+          // column phase: RPI whole rows per turn (lane = row in turn x 16-byte unit), one running pointer per lane
+          constexpr int RPI = 32 / UPR, TURNS = (32 + RPI - 1) / RPI;
+          const int rl0 = lane / UPR, u = lane - rl0 * UPR;
+          if (lane < RPI * UPR) {
+            const bool scat = p.sc.n_dst > 0;
+            bf16* base;
+            if (scat) {                                // this chunk (= one head) has one destination
+              const int part = c0 / p.sc.part_w, cc = c0 - part * p.sc.part_w, g = cc / p.sc.grp;
+              base = p.sc.dst[g] + part * p.sc.grp + (cc - g * p.sc.grp) + u * 8;
+            } else {
+              base = p.out + (r0 + rl0) * p.ldo + c0 + u * 8;
+            }
+#pragma unroll 1
+            for (int t = 0; t < TURNS; ++t) {
+              const int rl = t * RPI + rl0;
+              if (rl < 32 && r0 + rl < p.M) {
+                const uint4 val = *reinterpret_cast<const uint4*>(stg + rl * C::PITCH + u * 16);
+                bf16* optr = scat ? base + row_res[rl] : base + (int64_t)t * RPI * p.ldo;
+                *reinterpret_cast<uint4*>(optr) = val;
+              }
+            }
+          }
+          __syncwarp();
+          continue;
+        }
         // this chunk's residual / gate registers; the next chunk's loads go out before the TMEM data is consumed
         uint4 cres[NIT];
 #pragma unroll
@@ -288,24 +391,6 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           v[jj + 2] = __uint_as_float(raw[jj + 2]) + b4.z;
           v[jj + 3] = __uint_as_float(raw[jj + 3]) + b4.w;
         }
-        if constexpr (HD != 0) {
-          const int wsel = c0 < p.n_q ? 0 : (c0 < p.n_q + p.n_k ? 1 : 2);
-          if (wsel < 2) {
-            const float* w = s_rms + wsel * HD;
-            float ss = 0.f;
-#pragma unroll
-            for (int jj = 0; jj < CW; ++jj) ss += v[jj] * v[jj];
-            const float r = rsqrtf(ss / CW + p.eps);
-#pragma unroll
-            for (int jj = 0; jj < CW; jj += 4) {
-              const float4 w4 = *reinterpret_cast<const float4*>(w + jj);
-              v[jj + 0] = w4.x * __bfloat162float(__float2bfloat16_rn(v[jj + 0] * r));
-              v[jj + 1] = w4.y * __bfloat162float(__float2bfloat16_rn(v[jj + 1] * r));
-              v[jj + 2] = w4.z * __bfloat162float(__float2bfloat16_rn(v[jj + 2] * r));
-              v[jj + 3] = w4.w * __bfloat162float(__float2bfloat16_rn(v[jj + 3] * r));
-            }
-          }
-        }
         if (ep.act == 1) {
 #pragma unroll
           for (int jj = 0; jj < CW; ++jj) v[jj] = gelu_tanh_fast(v[jj]);
@@ -320,13 +405,6 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         __syncwarp();
         // column phase: coalesced 16-byte accesses: gate / residual / store
-        bf16* sc_base = nullptr;                     // scattered output: this chunk (= one head) has one destination
-        if constexpr (HD != 0) {
-          if (p.sc.n_dst > 0) {
-            const int part = c0 / p.sc.part_w, cc = c0 - part * p.sc.part_w, g = cc / p.sc.grp;
-            sc_base = p.sc.dst[g] + part * p.sc.grp + (cc - g * p.sc.grp);
-          }
-        }
 #pragma unroll
         for (int it = 0; it < NIT; ++it) {
           const int idx = lane + 32 * it, rl = idx / UPR, u = idx % UPR;
@@ -358,11 +436,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               }
               pk.pack(f);
             }
-            bf16* optr = p.out + gr * p.ldo + col;
-            if constexpr (HD != 0) {
-              if (sc_base != nullptr) optr = sc_base + row_res[rl] + u * 8;
-            }
-            *reinterpret_cast<uint4*>(optr) = pk.raw;
+            *reinterpret_cast<uint4*>(p.out + gr * p.ldo + col) = pk.raw;
           }
         }
         __syncwarp();
@@ -437,6 +511,29 @@ int mdv2_make_tmap_3d_heads(CUtensorMap* out, const void* ptr, uint64_t rows, ui
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     mdv2_set_error("cuTensorMapEncodeTiled(3d) failed (%d) ptr=%p rows=%llu H=%u D=%u ld=%llu", (int)r, ptr,
+                   (unsigned long long)rows, H, D, (unsigned long long)ld);
+    return MDV2_ECUDA;
+  }
+  return MDV2_OK;
+}
+
+// The 16-wide tail chunk (columns 64 .. 79, those past D zero-filled) of the same 3-D view as 32-byte rows, SW32.
+int mdv2_make_tmap_3d_heads_sw32(CUtensorMap* out, const void* ptr, uint64_t rows, uint32_t H, uint32_t D, uint64_t ld,
+                                 uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    mdv2_set_error("cuTensorMapEncodeTiled unavailable");
+    return MDV2_ECUDA;
+  }
+  cuuint64_t dims[3] = {D, H, rows};
+  cuuint64_t strides[2] = {(cuuint64_t)D * 2, ld * 2};
+  cuuint32_t box[3] = {16, 1, box_rows};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    mdv2_set_error("cuTensorMapEncodeTiled(3d sw32) failed (%d) ptr=%p rows=%llu H=%u D=%u ld=%llu", (int)r, ptr,
                    (unsigned long long)rows, H, D, (unsigned long long)ld);
     return MDV2_ECUDA;
   }
@@ -542,6 +639,11 @@ int launch(const CUtensorMap& ta, const CUtensorMap& ta_mc, const CUtensorMap& t
 
 int pick_bn(int N, const RmsArgs* rms) {
   if (rms && rms->wq) {
+    static const int heads3 = [] {                     // MDV2_GEMM_QKV216=0: two heads per tile (BN = 144)
+      const char* e = getenv("MDV2_GEMM_QKV216");
+      return e ? atoi(e) : 1;
+    }();
+    if (rms->head_dim == 72 && heads3 && N % 216 == 0) return 216;
     if (rms->head_dim == 72 && N % 144 == 0) return 144;
     if (rms->head_dim == 64 && N % 128 == 0) return 128;
     return 0;
@@ -584,7 +686,7 @@ int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void
   if (rc) return rc;
   rc = mdv2_make_tmap_2d(&ta_mc, a, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BM / 2, BK);     // 64-row boxes (multicast)
   if (rc) return rc;
-  rc = mdv2_make_tmap_2d(&tw, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)bn / 2, BK);
+  rc = mdv2_make_tmap_2d(&tw, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)(bn == 216 ? 224 : bn) / 2, BK);
   if (rc) return rc;
   CUtensorMap twr = tw;                                  // the narrow last column tile (N % bn columns): its own box height
   if (N % bn) {
@@ -595,7 +697,7 @@ int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void
   p.sc.n_dst = 0;
   if (scatter != nullptr) {
     const int hd = rms ? rms->head_dim : 0;
-    MDV2_REQUIRE(rms && rms->wq && (bn == 144 || bn == 128) && N % 3 == 0, "gemm_sm100: scattered output needs the RMSNorm qkv flavour");
+    MDV2_REQUIRE(rms && rms->wq && (bn == 216 || bn == 144 || bn == 128) && N % 3 == 0, "gemm_sm100: scattered output needs the RMSNorm qkv flavour");
     const int W = N / 3;
     MDV2_REQUIRE(scatter->n_dst >= 1 && scatter->n_dst <= 8 && W % scatter->n_dst == 0 && (W / scatter->n_dst) % hd == 0 &&
                      rms->n_q == W && rms->n_k == W && scatter->rows_per_seq > 0 && M % scatter->rows_per_seq == 0 &&
@@ -622,6 +724,7 @@ int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void
     case 256: return launch<256, 0>(ta, ta_mc, tw, twr, p, st);
     case 192: return launch<192, 0>(ta, ta_mc, tw, twr, p, st);
     case 64: return launch<64, 0>(ta, ta_mc, tw, twr, p, st);
+    case 216: return launch<216, 72>(ta, ta_mc, tw, twr, p, st);
     case 144: return launch<144, 72>(ta, ta_mc, tw, twr, p, st);
     case 128:
       if (rms && rms->wq) return launch<128, 64>(ta, ta_mc, tw, twr, p, st);

@@ -536,9 +536,17 @@ __device__ __forceinline__ void temporal_scores_mma_t8(uint8_t* rows, int pitch,
 // The strided gather / scatter never materialises the reference's two transposes (stdit3.py:232-234).
 // ------------------------------------------------------------------------------------------------
 constexpr int TA_G = 2, TA_THREADS = 256, TA_PAD = 80;
+// geometry of the short-clip kernel (tuning hooks for tools/gpu_temporal_variants.sh)
+#ifndef MDV2_TS_G
+#define MDV2_TS_G 2
+#define MDV2_TS_THREADS 256
+#define MDV2_TS_MINB 3
+#endif
+constexpr int TS_G = MDV2_TS_G, TS_THREADS = MDV2_TS_THREADS, TS_MINB = MDV2_TS_MINB;
+constexpr int TS_SMEM_MAX = TS_MINB == 3 ? 75 * 1024 : (227 * 1024) / TS_MINB - 1024;
 
 template <int TN>
-__global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_kernel(const bf16* __restrict__ qkv, int64_t ld,
+__global__ void __launch_bounds__(TS_THREADS, TS_MINB) temporal_attn_smem_kernel(const bf16* __restrict__ qkv, int64_t ld,
                                                                           const float* __restrict__ cos_t,
                                                                           const float* __restrict__ sin_t,
                                                                           bf16* __restrict__ out, int64_t ldo,
@@ -548,10 +556,10 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_kernel(const
   extern __shared__ __align__(128) uint8_t ta_smem[];
   const int C = H * D;
   const int row_bytes = 3 * C * 2, pitch = row_bytes + TA_PAD;
-  uint64_t* bar = reinterpret_cast<uint64_t*>(ta_smem + TA_G * TN * pitch);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(ta_smem + TS_G * TN * pitch);
   const int tid = threadIdx.x;
-  const int64_t col0 = (int64_t)blockIdx.x * TA_G;
-  const int ng = (int)((n_cols - col0) < TA_G ? (n_cols - col0) : TA_G);
+  const int64_t col0 = (int64_t)blockIdx.x * TS_G;
+  const int ng = (int)((n_cols - col0) < TS_G ? (n_cols - col0) : TS_G);
   auto grow = [&](int g, int t) {                       // global row of (column col0+g, frame t)
     const int64_t c = col0 + g, beta = c / S, s = c - beta * S;
     return (beta * TN + t) * S + s;
@@ -574,7 +582,7 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_kernel(const
   // columns: the head-dimension offset is divided out once per thread and the cos / sin vectors are loaded once per
   // frame.  (One flat index over (column, frame, part, vector) cost 181 instructions per vector, 59 % of the kernel's
   // instructions, most of them the four runtime divisions and the angle loads.)
-  for (int u = tid; u < 2 * vpr; u += TA_THREADS) {
+  for (int u = tid; u < 2 * vpr; u += TS_THREADS) {
     const bool is_q = u < vpr;
     const int d0 = ((is_q ? u : u - vpr) % vph) * 8;
 #pragma unroll
@@ -586,7 +594,7 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_kernel(const
       const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
       const float sn[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
 #pragma unroll
-      for (int g = 0; g < TA_G; ++g) {
+      for (int g = 0; g < TS_G; ++g) {
         if (g < ng) {
           uint4* ptr = reinterpret_cast<uint4*>(ta_smem + (g * TN + t) * pitch + u * 16);
           Vec16<bf16> x;
@@ -613,14 +621,14 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_kernel(const
   __syncthreads();
   if (use_mma == 1) {
     // ---- B + C on the tensor cores (mma.sync tiles, one warp per (column, head); see temporal_head_mma) ----
-    for (int idx = tid >> 5; idx < ng * H; idx += TA_THREADS / 32) {
+    for (int idx = tid >> 5; idx < ng * H; idx += TS_THREADS / 32) {
       const int h = idx % H, g = idx / H;
       temporal_head_mma(ta_smem + g * TN * pitch + h * D * 2, pitch, C * 2, TN, D);
     }
   } else {
   // ---- B: scores + softmax; P[t_q][0..TN) -> first bytes of the q slice of row t_q ----
   if (use_mma == 2) {                                   // one warp per (column, head): one m16n8 tile (opt-in)
-    for (int idx = tid >> 5; idx < ng * H; idx += TA_THREADS / 32) {
+    for (int idx = tid >> 5; idx < ng * H; idx += TS_THREADS / 32) {
       const int h = idx % H, g = idx / H;
       temporal_scores_mma_t8<TN>(ta_smem + g * TN * pitch + h * D * 2, pitch, C * 2, D);
     }
@@ -667,7 +675,7 @@ __global__ void __launch_bounds__(TA_THREADS, 3) temporal_attn_smem_kernel(const
   }
   __syncthreads();
   // ---- C: out[t_q][8 dims] = sum_k P[t_q][k] v[k][8 dims], written over the k part of row t_q ----
-  for (int i = tid; i < ng * H * vph; i += TA_THREADS) {
+  for (int i = tid; i < ng * H * vph; i += TS_THREADS) {
     const int j = i % vph, h = (i / vph) % H, g = i / (vph * H);
     float v[TN][8];
 #pragma unroll
@@ -890,13 +898,13 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
   const int64_t n_warps = (int64_t)B * S * H;
   if constexpr (sizeof(T) == 2) {
     const int C = H * D;
-    const size_t smem = (size_t)TA_G * Tn * (3 * C * 2 + TA_PAD) + 16;
+    const size_t smem = (size_t)TS_G * Tn * (3 * C * 2 + TA_PAD) + 16;
     static const bool legacy = getenv("MDV2_TEMPORAL_LEGACY") != nullptr;       // tuning hook (tools/bench_elem.py)
     if (!legacy && Tn <= 8 && D % 8 == 0 && D * 2 >= 32 && ld % 8 == 0 && ldo % 8 == 0 && ((uintptr_t)qkv % 16 == 0) &&
-        ((uintptr_t)out % 16 == 0) && ((uintptr_t)c % 16 == 0) && ((uintptr_t)s % 16 == 0) && smem <= 75 * 1024 &&
-        TA_G * H * Tn <= TA_THREADS) {
+        ((uintptr_t)out % 16 == 0) && ((uintptr_t)c % 16 == 0) && ((uintptr_t)s % 16 == 0) && smem <= (size_t)TS_SMEM_MAX &&
+        TS_G * H * Tn <= TS_THREADS) {
       const int64_t n_cols = (int64_t)B * S;
-      const unsigned nb = (unsigned)((n_cols + TA_G - 1) / TA_G);
+      const unsigned nb = (unsigned)((n_cols + TS_G - 1) / TS_G);
       // A/B hook: 0 scalar scores (default), 1 tensor-core scores AND P·V (temporal_head_mma), 2 tensor-core scores.
       // Measured at T = 5, 67 200 columns: 0.874 / 1.202 / 1.016 ms — one warp per head is a chain of five dependent
       // mma.sync on one accumulator; the scalar phase keeps 160 threads busy instead
@@ -908,10 +916,10 @@ static int launch_temporal(const void* qkv, int64_t ld, const float* c, const fl
   case TT: {                                                                                                      \
     static PerDeviceFlag configured_flag; bool& configured = configured_flag.here();                                                                               \
     if (!configured) {                                                                                            \
-      cudaFuncSetAttribute(temporal_attn_smem_kernel<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024); \
+      cudaFuncSetAttribute(temporal_attn_smem_kernel<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_MAX); \
       configured = true;                                                                                          \
     }                                                                                                             \
-    temporal_attn_smem_kernel<TT><<<nb, TA_THREADS, smem, st>>>((const bf16*)qkv, ld, c, s, (bf16*)out, ldo, n_cols, \
+    temporal_attn_smem_kernel<TT><<<nb, TS_THREADS, smem, st>>>((const bf16*)qkv, ld, c, s, (bf16*)out, ldo, n_cols, \
                                                                S, H, D, scale, short_mma);                        \
   } break
       switch (Tn) {

@@ -193,6 +193,16 @@ __device__ __forceinline__ uint64_t make_desc_k_sw128(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
   return d;
 }
+// K-major operand, 32-byte swizzle: rows are 32 B (16 bf16 = one k16 step), 8-row groups are 256 B apart.
+__device__ __forceinline__ uint64_t make_desc_k_sw32(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(256 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)6 << 61;                        // SWIZZLE_32B
+  return d;
+}
 // MN-major operand, 128-byte swizzle: 64 contiguous MN elements per 128-B row, 8 K-rows per 1024-B atom.
 // lbo = byte distance between 64-element MN chunks, sbo = byte distance between 8-row K groups.
 __device__ __forceinline__ uint64_t make_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
