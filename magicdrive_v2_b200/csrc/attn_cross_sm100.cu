@@ -42,7 +42,16 @@ constexpr int BNK = 64;           // keys per K/V tile = all of them
 // Rings: Q is the only operand that comes from DRAM (K / V of a sequence are 0.3 MB and L2-resident), and at ~1.5 us of
 // loaded DRAM latency an SM needs ~65 KB of reads in flight to draw its share of the bandwidth: Q runs Q_AHEAD items
 // ahead of K.  (With a 3-slot Q ring and one in-order producer stream the issuer spent 31 % of its time waiting for Q.)
-constexpr int Q_SLOTS = 6, K_SLOTS = 3, V_SLOTS = 2, Q_AHEAD = Q_SLOTS - K_SLOTS;
+#ifndef MDV2_XATTN_QS
+#define MDV2_XATTN_QS 5
+#define MDV2_XATTN_VS 3
+#endif
+constexpr int Q_SLOTS = MDV2_XATTN_QS, K_SLOTS = 3, V_SLOTS = MDV2_XATTN_VS, Q_AHEAD = Q_SLOTS - K_SLOTS;
+#ifndef MDV2_XATTN_LSU_STORE
+#define MDV2_XATTN_LSU_STORE 0
+#endif
+constexpr bool LSU_STORE = MDV2_XATTN_LSU_STORE != 0;   // output rows by coalesced st.global instead of TMA stores
+constexpr int V_LAG = V_SLOTS == 3 ? 1 : 2;      // step i requests V(i - V_LAG): its slot comes back with P·V(i - 4)
 constexpr int N_SM_WARPS = 8;     // two groups of four
 constexpr int NTHREADS = (2 + N_SM_WARPS) * 32;
 constexpr int TMEM_COLS = 512;    // S_b (P_b over it) at 128·b, O_b at 256 + 128·b
@@ -69,7 +78,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
 attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
                   const __grid_constant__ CUtensorMap tv, const __grid_constant__ CUtensorMap to,
                   const __grid_constant__ CUtensorMap tq1, const __grid_constant__ CUtensorMap tk1, const AParams p,
-                  const int n_qt, const int n_items) {
+                  const int n_qt, const int n_items, const int teams) {
   using C = XCfg<DP>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -92,9 +101,31 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   // this CTA's contiguous range of items; item -> (sequence, query tile, head), head fastest
+  // Work split.  teams > 0 (experiment, off: see the launcher): the grid is `teams` teams of H CTAs; a team walks the
+  // 128-row query blocks (sequence, query tile) team, team + teams, ... and CTA j of the team owns head j of every block —
+  // the H slices of a row block are wanted by H SMs at about the same time (DRAM sees whole rows, L2 serves the
+  // neighbours' sectors) and a CTA's head never changes.  teams == 0 (default): a contiguous range of (sequence, query
+  // tile, head) items per CTA, head fastest.
   const int64_t G = gridDim.x;
-  const int i0 = (int)((int64_t)n_items * blockIdx.x / G), i1 = (int)((int64_t)n_items * (blockIdx.x + 1) / G);
-  const int n_my = i1 - i0;
+  const int team = teams > 0 ? (int)blockIdx.x / p.H : 0, my_head = teams > 0 ? (int)blockIdx.x % p.H : 0;
+  const int n_rb = n_items / p.H;                       // row blocks
+  const int i0 = teams > 0 ? 0 : (int)((int64_t)n_items * blockIdx.x / G);
+  const int n_my = teams > 0 ? (n_rb - team + teams - 1) / teams
+                             : (int)((int64_t)n_items * (blockIdx.x + 1) / G) - i0;
+  // local item i -> (head, query tile, sequence)
+  auto coords = [&](int i, int& h, int& qt, int& seq) {
+    int r;
+    if (teams > 0) {
+      h = my_head;
+      r = team + teams * i;
+    } else {
+      const int it = i0 + i;
+      r = it / p.H;
+      h = it - r * p.H;
+    }
+    seq = r / n_qt;
+    qt = r - seq * n_qt;
+  };
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tq);
@@ -133,17 +164,26 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
 
   if (warp == 0) {
     // ================= TMA producer =================
-    // step i requests Q(i + Q_AHEAD) and K(i) — both slots come back when Q·K^T(i - K_SLOTS) has completed — and then
-    // V(i - 2), whose slot P·V(i - 4) returns a little later; nothing a DRAM read is queued behind waits for long
+    // step i requests V(i - V_LAG) — its slot comes back with P·V(i - 4) — then K(i) and Q(i + Q_AHEAD), whose slots came
+    // back earlier, with Q·K^T(i - K_SLOTS).  V goes first: the copy engine serves requests in order, and a V tile queued
+    // behind 384 row requests of Q and K reached the issuer late (it waited for V 37 % of its time, ncu)
     if (lane == 0) {
-      auto coords = [&](int i, int& h, int& qt, int& seq) {
-        const int it = i0 + i, r = it / p.H;
-        h = it - r * p.H;
-        seq = r / n_qt;
-        qt = r - seq * n_qt;
-      };
       for (int i = -Q_AHEAD; i < n_my + 2; ++i) {
         int h, qt, seq;
+        const int jv = i - V_LAG;                      // first: V is the load with the least slack
+        if (jv >= 0 && jv < n_my) {
+          coords(jv, h, qt, seq);
+          const int vs = jv % V_SLOTS;
+          mbar_wait_hint(&v_empty[vs], (uint32_t)(((jv / V_SLOTS) & 1) ^ 1), TMA_HINT);
+          if ((p.dbg & 1) && jv >= V_SLOTS) {
+            mbar_arrive(&v_full[vs]);
+          } else {
+            mbar_expect_tx(&v_full[vs], C::V_BYTES);
+#pragma unroll
+            for (int c = 0; c < (C::TAIL ? 2 : 1); ++c)
+              tma_load_3d(sV + vs * C::V_BYTES + c * BNK * 128, &tv, &v_full[vs], c * 64, h, seq * p.Lk);
+          }
+        }
         const int jq = i + Q_AHEAD;
         if (jq < n_my) {
           coords(jq, h, qt, seq);
@@ -169,20 +209,6 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
             mbar_expect_tx(&k_full[ks], C::K_BYTES);
             tma_load_3d(dst, &tk, &k_full[ks], 0, h, seq * p.Lk);
             if (C::TAIL) tma_load_3d(dst + C::K_MAIN, &tk1, &k_full[ks], 64, h, seq * p.Lk);
-          }
-        }
-        const int jv = i - 2;
-        if (jv >= 0 && jv < n_my) {
-          coords(jv, h, qt, seq);
-          const int vs = jv % V_SLOTS;
-          mbar_wait_hint(&v_empty[vs], (uint32_t)(((jv / V_SLOTS) & 1) ^ 1), TMA_HINT);
-          if ((p.dbg & 1) && jv >= V_SLOTS) {
-            mbar_arrive(&v_full[vs]);
-          } else {
-            mbar_expect_tx(&v_full[vs], C::V_BYTES);
-#pragma unroll
-            for (int c = 0; c < (C::TAIL ? 2 : 1); ++c)
-              tma_load_3d(sV + vs * C::V_BYTES + c * BNK * 128, &tv, &v_full[vs], c * 64, h, seq * p.Lk);
           }
         }
       }
@@ -242,12 +268,7 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
     // (sequence, query tile, head) of the warp's current item, stepped by two items per turn: four runtime divisions
     // per item were 7 % of the kernel's instructions, on the chain between two tiles
     int h, qt, seq;
-    {
-      const int it = i0 + b, rr = it / p.H;
-      h = it - rr * p.H;
-      seq = rr / n_qt;
-      qt = rr - seq * n_qt;
-    }
+    coords(b, h, qt, seq);
     for (int i = b; i < n_my; i += 2) {
       const uint32_t ph = (uint32_t)((i >> 1) & 1);
       mbar_wait(&s_full[b], ph);
@@ -300,8 +321,10 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[b]);
       // ---- O = P·V back, normalised, through shared memory, one TMA store per warp ----
-      if (lane == 0) bulk_wait_read0();                  // the warp's previous store (two items ago) has left shared memory
-      __syncwarp();
+      if constexpr (!LSU_STORE) {
+        if (lane == 0) bulk_wait_read0();                // the warp's previous store (two items ago) has left shared memory
+        __syncwarp();
+      }
       mbar_wait(&o_full[b], ph);
       tc_fence_after();
       if (quarter == 0 && lane == 0) mbar_arrive(&v_empty[i % V_SLOTS]);   // P·V has completed: V goes back
@@ -325,23 +348,50 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
         const int uu = DP == 64 ? (u ^ (lane & 7)) : u;
         *reinterpret_cast<uint4*>(srow + uu * 16) = o.raw;
       }
-      fence_async_smem();                                // generic-proxy writes -> the copy engine
-      __syncwarp();
-      if (lane == 0) {
+      if constexpr (LSU_STORE) {
+        // rows back out of the staging buffer with coalesced 16-byte stores (whole 144-byte row pieces per warp turn)
+        __syncwarp();
+        constexpr int UPR = C::ROW_BYTES / 16;
         const int r0 = qt * BMQ + quarter * 32;
-        if (r0 < p.Lq && !(p.dbg & 2)) tma_store_4d(&to, swarp, 0, h, r0, seq);
-        bulk_commit();
+        bf16* obase = p.out + ((int64_t)seq * p.Lq + r0) * p.ldo + (int64_t)h * p.D;
+        if (!(p.dbg & 2)) {
+#pragma unroll
+          for (int t = 0; t < UPR; ++t) {
+            const int idx = lane + 32 * t, rl = idx / UPR, u = idx - rl * UPR;
+            const int uu = DP == 64 ? (u ^ (rl & 7)) : u;
+            if (r0 + rl < p.Lq)
+              *reinterpret_cast<uint4*>(obase + (int64_t)rl * p.ldo + u * 8) =
+                  *reinterpret_cast<const uint4*>(swarp + rl * C::ROW_BYTES + uu * 16);
+          }
+        }
+        __syncwarp();
+      } else {
+        fence_async_smem();                              // generic-proxy writes -> the copy engine
+        __syncwarp();
+        if (lane == 0) {
+          const int r0 = qt * BMQ + quarter * 32;
+          if (r0 < p.Lq && !(p.dbg & 2)) tma_store_4d(&to, swarp, 0, h, r0, seq);
+          bulk_commit();
+        }
       }
-      h += 2;
-      while (h >= p.H) {
-        h -= p.H;
-        if (++qt == n_qt) {
-          qt = 0;
+      if (teams > 0) {
+        qt += 2 * teams;
+        while (qt >= n_qt) {
+          qt -= n_qt;
           ++seq;
+        }
+      } else {
+        h += 2;
+        while (h >= p.H) {
+          h -= p.H;
+          if (++qt == n_qt) {
+            qt = 0;
+            ++seq;
+          }
         }
       }
     }
-    if (lane == 0) bulk_wait_read0();                    // shared memory must outlive the engine's reads
+    if (!LSU_STORE && lane == 0) bulk_wait_read0();      // shared memory must outlive the engine's reads
   }
   tc_fence_before();
   __syncthreads();
@@ -378,7 +428,21 @@ int launch_cross(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap
   MDV2_REQUIRE(n_items <= 0x7fffffff, "attention_cross: too many work items");
   int64_t grid = mdv2_num_sms();
   if (grid > n_items) grid = n_items;
-  attn_cross_kernel<DP><<<(unsigned)grid, NTHREADS, SMEM, st>>>(tq, tk, tv, to, tq1, tk1, p, n_qt, (int)n_items);
+  // MDV2_ATTN_CROSS_TEAMS=1: teams of H CTAs in lock-step on one row block (see the kernel).  Measured 0.52 ms against
+  // 0.36 ms for contiguous item ranges at 60 x 5600 x 62: sixteen SMs asking for the same 128 rows at the same moment
+  // queue on the same L2 slices / DRAM pages instead of sharing them.  Off.
+  static const int team_mode = [] {
+    const char* e = getenv("MDV2_ATTN_CROSS_TEAMS");
+    return e ? atoi(e) : 0;
+  }();
+  int teams = 0;
+  if (team_mode && p.H <= mdv2_num_sms()) {
+    teams = mdv2_num_sms() / p.H;
+    const int64_t n_rb = (int64_t)n_qt * n_seq;
+    if (teams > n_rb) teams = (int)n_rb;
+    grid = (int64_t)teams * p.H;
+  }
+  attn_cross_kernel<DP><<<(unsigned)grid, NTHREADS, SMEM, st>>>(tq, tk, tv, to, tq1, tk1, p, n_qt, (int)n_items, teams);
   MDV2_CHECK_LAUNCH("attention_cross");
   return MDV2_OK;
 }
