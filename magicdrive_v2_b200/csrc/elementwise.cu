@@ -3,6 +3,7 @@
 #include <stdarg.h>
 
 #include "common.cuh"
+#include "sm100_ptx.cuh"
 
 static thread_local char g_err[512] = "";
 void mdv2_set_error(const char* fmt, ...) {
@@ -72,31 +73,38 @@ __global__ void __launch_bounds__(LN_WARPS * 32, VPL <= 5 ? 3 : 1) ln_modulate_k
     if (row + LN_WARPS < row_end) load_row(row + LN_WARPS, nxt);
     // the row stays PACKED in registers (cur) and is unpacked once per pass: three cheap unpacks instead of
     // 8 live fp32 values per vector keep the kernel at 4 CTAs/SM
-    float sum = 0.f;
+    // packed fp32 pairs (FADD2 / FFMA2 / FMUL2: two results per issue slot): inside the power-capped step the SM clock
+    // drops to ~1.45 GHz and the ~10 scalar instructions per element of the three passes, not HBM, set this kernel's pace
+    using sm100::fadd2;
+    using sm100::ffma2;
+    using sm100::fmul2;
+    float2 sum2 = make_float2(0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < VPL; ++i) {
       if (lane + 32 * i < nvec) {
         float v[VN];
         cur[i].unpack(v);
 #pragma unroll
-        for (int j = 0; j < VN; ++j) sum += v[j];
+        for (int j = 0; j < VN; j += 2) sum2 = fadd2(sum2, make_float2(v[j], v[j + 1]));
       }
     }
-    const float mean = warp_sum(sum) / C;
-    float sq = 0.f;
+    const float mean = warp_sum(sum2.x + sum2.y) / C;
+    const float2 nmean2 = make_float2(-mean, -mean);
+    float2 sq2 = make_float2(0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < VPL; ++i) {
       if (lane + 32 * i < nvec) {
         float v[VN];
         cur[i].unpack(v);
 #pragma unroll
-        for (int j = 0; j < VN; ++j) {
-          const float dlt = v[j] - mean;
-          sq += dlt * dlt;
+        for (int j = 0; j < VN; j += 2) {
+          const float2 dlt = fadd2(make_float2(v[j], v[j + 1]), nmean2);
+          sq2 = ffma2(dlt, dlt, sq2);
         }
       }
     }
-    const float rstd = rsqrtf(warp_sum(sq) / C + eps);
+    const float rstd = rsqrtf(warp_sum(sq2.x + sq2.y) / C + eps);
+    const float2 rstd2 = make_float2(rstd, rstd);
     const uint32_t tab = table_row(row);
     const bool staged = tab == tab0;
     const float* mrow = mod + (int64_t)tab * K * C;
@@ -120,10 +128,14 @@ __global__ void __launch_bounds__(LN_WARPS * 32, VPL <= 5 ? 3 : 1) ln_modulate_k
             s4 = *reinterpret_cast<const float4*>(gsc + vi * VN + j);
             s4.x += 1.f; s4.y += 1.f; s4.z += 1.f; s4.w += 1.f;
           }
-          o[j + 0] = (v[j + 0] - mean) * rstd * s4.x + h4.x;
-          o[j + 1] = (v[j + 1] - mean) * rstd * s4.y + h4.y;
-          o[j + 2] = (v[j + 2] - mean) * rstd * s4.z + h4.z;
-          o[j + 3] = (v[j + 3] - mean) * rstd * s4.w + h4.w;
+          const float2 o01 = ffma2(fmul2(fadd2(make_float2(v[j + 0], v[j + 1]), nmean2), rstd2),
+                                   make_float2(s4.x, s4.y), make_float2(h4.x, h4.y));
+          const float2 o23 = ffma2(fmul2(fadd2(make_float2(v[j + 2], v[j + 3]), nmean2), rstd2),
+                                   make_float2(s4.z, s4.w), make_float2(h4.z, h4.w));
+          o[j + 0] = o01.x;
+          o[j + 1] = o01.y;
+          o[j + 2] = o23.x;
+          o[j + 3] = o23.y;
         }
         Vec16<T> t;
         t.pack(o);

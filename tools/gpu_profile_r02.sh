@@ -1,5 +1,5 @@
 #!/bin/bash
-# round-2 ncu evidence: launch list of ONE bracketed step of the bench command, --set full captures of the two dominant
+# round-2 ncu evidence: launch list of ONE bracketed step of the bench command, --set full captures of the dominant
 # kernels (the command runs plain first; ncu only if it exits 0)
 mkdir -p gpurun_out
 CMD="python bench.py --steps 1 --warmup 3 --no-secondary --no-cpu-baseline"
@@ -13,4 +13,7 @@ echo "attn rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off \
     -k regex:gemm_sm100_kernel -s 200 -c 8 -o gpurun_out/prof_gemm_r02 -f $CMD > gpurun_out/ncu_gemm.log 2>&1
 echo "gemm rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off \
+    -k "regex:attn_cross_kernel|temporal_attn_smem_kernel|ln_modulate_kernel" -s 30 -c 6 -o gpurun_out/prof_hbm_r02 -f $CMD > gpurun_out/ncu_hbm.log 2>&1
+echo "hbm kernels rc=$?"
 ls -la gpurun_out | tail -8
