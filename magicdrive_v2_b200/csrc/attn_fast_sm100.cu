@@ -483,9 +483,12 @@ int launch_fast(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap&
 // called by mdv2_attention_sm100 (attn_sm100.cu) for K/V sequences longer than 64 keys
 int mdv2_attention_fast_launch(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AParams& p,
                                int n_seq, int D, bool trace, cudaStream_t st) {
-  static const int pf = [] {                             // tuning hook: polynomial pairs per 8 (tools/bench_attn.py)
+  // polynomial pairs per 8 (tuning hook, tools/bench_attn.py).  Alone at full clocks 3 is the fastest setting by ~1 %; inside
+  // the power-capped step (1.40-1.55 GHz) 2 is: 1127 ms of attention per step against 1146-1151 (3), 1165 (0), 1212 (4) in
+  // a same-box sweep (profiles/attn_pf_instep_r02.txt) — the polynomial's FMA-pipe instructions cost clock under the cap
+  static const int pf = [] {
     const char* e = getenv("MDV2_ATTN_PF");
-    return e ? atoi(e) : 3;
+    return e ? atoi(e) : 2;
   }();
   if (D == 72) {
     if (trace) return launch_fast<80, 3, true>(tq, tk, tv, p, n_seq, st);
