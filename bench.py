@@ -220,7 +220,7 @@ def workload_config(name, p):
 class ClockSampler:
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_power_cap,clocks.mem")
 
     def __init__(self, index):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
@@ -242,7 +242,7 @@ class ClockSampler:
         self.f.flush()
         rows = [r.strip().split(", ") for r in open(self.f.name) if r.strip()]
         os.unlink(self.f.name)
-        sm, mx, pw, reasons = [], [], [], set()
+        sm, mx, pw, mem, reasons = [], [], [], [], set()
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
         for r in rows:
             try:
@@ -252,10 +252,14 @@ class ClockSampler:
             for n, v in zip(names, r[3:7]):
                 if v.strip().lower().startswith("active"):
                     reasons.add(n)
+            try:
+                mem.append(float(r[7]))
+            except (ValueError, IndexError):
+                pass
         if not sm:
             return dict(sm_mhz=None, sm_max_mhz=None, reasons=["no samples"])
         return dict(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), power_w_max=max(pw), samples=len(sm),
-                    reasons=sorted(reasons))
+                    mem_mhz=statistics.median(mem) if mem else None, reasons=sorted(reasons))
 
 
 def build_model(wl_name, device, sp):
