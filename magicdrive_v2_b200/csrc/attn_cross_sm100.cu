@@ -81,7 +81,8 @@ attn_cross_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
                   const int n_qt, const int n_items, const int teams) {
   using C = XCfg<DP>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // (pointer arithmetic on the __shared__ array keeps the address space: the staging stores stay STS, not generic ST.E)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sQ = smem;                                   // slot s at sQ + s·Q_BYTES
   uint8_t* sK = sQ + Q_SLOTS * C::Q_BYTES;              // slot s at sK + s·K_BYTES
   uint8_t* sV = sK + K_SLOTS * C::K_BYTES;

@@ -486,7 +486,12 @@ attn_pers_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
                  const int n_items) {
   using C = PCfg<DP>;
   extern __shared__ uint8_t smem_raw[];
+#ifdef MDV2_SMEM_GENERIC                               // A/B hook: the previous form (loses the address space)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+#else
+  // pointer arithmetic on the __shared__ array keeps the address space (LDS / STS instead of generic LD.E / ST.E)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+#endif
   const Lay<DP> L(smem);
   uint8_t *const sK = L.sK, *const sV = L.sV;
   uint64_t *const bars = L.k_full, *const k_full = L.k_full, *const k_empty = L.k_empty, *const v_full = L.v_full,

@@ -82,7 +82,12 @@ attn_sm100_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant_
   using SH = AShape<BNK>;
   constexpr int QT = SH::QT, TMEM_COLS = SH::TMEM_COLS;
   extern __shared__ uint8_t smem_raw[];
+#ifdef MDV2_SMEM_GENERIC                               // A/B hook: the previous form (loses the address space)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+#else
+  // pointer arithmetic on the __shared__ array keeps the address space (LDS / STS instead of generic LD.E / ST.E)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+#endif
   constexpr int KV_STAGES = C::KV_STAGES;
   uint8_t* sK = smem;                                   // stage s at sK + s·KV_BYTES
   uint8_t* sV = sK + KV_STAGES * C::KV_BYTES;

@@ -86,7 +86,10 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                   const __grid_constant__ CUtensorMap tmap_wr, const Params p) {
   using C = Cfg<BN, HD>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // aligned up to 1024 B by POINTER arithmetic on the __shared__ array: a round trip through uintptr_t loses the address
+  // space, and every staging access of the epilogue became a generic LD.E / ST.E (long-scoreboard, ~5x the latency of
+  // LDS: the dependent staging load of the column phase was 15 % of the gate + residual GEMMs' stall samples)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* staging = smem + C::STAGES * C::STAGE_BYTES;
   uint32_t* s_rms = reinterpret_cast<uint32_t*>(staging + C::STAGING);   // [2][HD / 2]: q, k RMSNorm weights as bf16 pairs
   uint64_t* bars = reinterpret_cast<uint64_t*>(staging + C::STAGING + C::RMSW);
