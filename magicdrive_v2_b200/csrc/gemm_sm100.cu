@@ -247,12 +247,24 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           }
         }
       }
+      if constexpr (CW == 32) {
+        // one bias element per lane and chunk: all of them requested before the first is converted (a load, its
+        // conversion and its store per chunk exposed the L2 latency CPW times per tile)
+        bf16 bv[CPW];
 #pragma unroll
-      for (int ci = 0; ci < CPW; ++ci) {
-        const int c0 = n0 + (half + 2 * ci) * CW;
-        if (ci < n_ci)
-          for (int jj = lane; jj < CW; jj += 32)
-            sbias[ci * CW + jj] = ep.bias ? ep.bias_scale * __bfloat162float(ep.bias[c0 + jj]) : 0.f;
+        for (int ci = 0; ci < CPW; ++ci)
+          if (ep.bias && ci < n_ci) bv[ci] = ep.bias[n0 + (half + 2 * ci) * CW + lane];
+#pragma unroll
+        for (int ci = 0; ci < CPW; ++ci)
+          if (ci < n_ci) sbias[ci * CW + lane] = ep.bias ? ep.bias_scale * __bfloat162float(bv[ci]) : 0.f;
+      } else {
+#pragma unroll
+        for (int ci = 0; ci < CPW; ++ci) {
+          const int c0 = n0 + (half + 2 * ci) * CW;
+          if (ci < n_ci)
+            for (int jj = lane; jj < CW; jj += 32)
+              sbias[ci * CW + jj] = ep.bias ? ep.bias_scale * __bfloat162float(ep.bias[c0 + jj]) : 0.f;
+        }
       }
       __syncwarp();
       const bool gate_uniform = FIXED_U && has_gate && row_gate[0] == row_gate[31];
@@ -407,14 +419,21 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           *reinterpret_cast<uint4*>(srow + jj * 2) = pk.raw;
         }
         __syncwarp();
-        // column phase: coalesced 16-byte accesses: gate / residual / store
+        // column phase: coalesced 16-byte accesses: gate / residual / store.  The staged vectors of all turns are read
+        // first (the row guard kept the compiler from hoisting them: four exposed LDS latencies per chunk)
+        uint4 spk[NIT];
+#pragma unroll
+        for (int it = 0; it < NIT; ++it) {
+          const int idx = lane + 32 * it;
+          spk[it] = *reinterpret_cast<const uint4*>(stg + (idx / UPR) * C::PITCH + (idx % UPR) * 16);
+        }
 #pragma unroll
         for (int it = 0; it < NIT; ++it) {
           const int idx = lane + 32 * it, rl = idx / UPR, u = idx % UPR;
           const int64_t gr = r0 + rl;
           if (gr < p.M) {
             Vec16<bf16> pk;
-            pk.raw = *reinterpret_cast<const uint4*>(stg + rl * C::PITCH + u * 16);
+            pk.raw = spk[it];
             const int col = c0 + u * 8;
             if (has_gate || has_res) {
               float f[8];
