@@ -635,9 +635,10 @@ __global__ void __launch_bounds__(TS_THREADS, TS_MINB) temporal_attn_smem_kernel
   } else if (tid < ng * H * TN) {                       // default: one thread per (column, head, t_q)
     const int tq = tid % TN, h = (tid / TN) % H, g = tid / (TN * H);
     const uint8_t* qs = ta_smem + (g * TN + tq) * pitch + h * D * 2;
-    float acc[TN];
+    // dot products on packed fp32 pairs (FFMA2: even / odd dimensions accumulate separately, added at the end)
+    float2 acc2[TN];
 #pragma unroll
-    for (int t = 0; t < TN; ++t) acc[t] = 0.f;
+    for (int t = 0; t < TN; ++t) acc2[t] = make_float2(0.f, 0.f);
     for (int j = 0; j < vph; ++j) {
       Vec16<bf16> qv;
       qv.raw = *reinterpret_cast<const uint4*>(qs + j * 16);
@@ -650,9 +651,13 @@ __global__ void __launch_bounds__(TS_THREADS, TS_MINB) temporal_attn_smem_kernel
         float k[8];
         kv.unpack(k);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) acc[t] += q[e] * k[e];
+        for (int e = 0; e < 8; e += 2)
+          acc2[t] = sm100::ffma2(make_float2(q[e], q[e + 1]), make_float2(k[e], k[e + 1]), acc2[t]);
       }
     }
+    float acc[TN];
+#pragma unroll
+    for (int t = 0; t < TN; ++t) acc[t] = acc2[t].x + acc2[t].y;
     float mx = -INFINITY;
 #pragma unroll
     for (int t = 0; t < TN; ++t) {
@@ -693,12 +698,16 @@ __global__ void __launch_bounds__(TS_THREADS, TS_MINB) temporal_attn_smem_kernel
         const float4 p1 = pp[1];
         pr[4] = p1.x; pr[5] = p1.y; pr[6] = p1.z; pr[7] = p1.w;
       }
-      float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      float2 o2[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) o2[e] = make_float2(0.f, 0.f);
 #pragma unroll
       for (int t = 0; t < TN; ++t) {
+        const float2 pt = make_float2(pr[t], pr[t]);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) o[e] += pr[t] * v[t][e];
+        for (int e = 0; e < 4; ++e) o2[e] = sm100::ffma2(pt, make_float2(v[t][2 * e], v[t][2 * e + 1]), o2[e]);
       }
+      const float o[8] = {o2[0].x, o2[0].y, o2[1].x, o2[1].y, o2[2].x, o2[2].y, o2[3].x, o2[3].y};
       Vec16<bf16> ov;
       ov.pack(o);
       *reinterpret_cast<uint4*>(ta_smem + (g * TN + tq) * pitch + C * 2 + h * D * 2 + j * 16) = ov.raw;

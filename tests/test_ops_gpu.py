@@ -93,6 +93,11 @@ def test_gemm_tcgen05_epilogues():
     assert _gemm_case(bf, 1000, 3456, 1152, "tcgen05", rms=(72, 1152, 1152)) < tol
     assert _gemm_case(bf, 1000, 3456, 1152, "tcgen05", bias=False, rms=(72, 1152, 1152)) < tol
     assert _gemm_case(bf, 700, 1152, 384, "tcgen05", rms=(64, 384, 384)) < tol
+    # three heads per tile (BN = 216, the MMA runs 224 wide and reads 8 rows of W past the tile): tiles that straddle the
+    # q | k | v boundaries, a last tile whose extra rows are TMA zero fill, M not a multiple of the 256-row pair tile
+    assert _gemm_case(bf, 300, 648, 128, "tcgen05", rms=(72, 216, 216)) < tol
+    assert _gemm_case(bf, 77, 432, 64, "tcgen05", rms=(72, 144, 144)) < tol
+    assert _gemm_case(bf, 513, 1080, 192, "tcgen05", bias=False, rms=(72, 360, 360)) < tol
 
 
 def test_gemm_tcgen05_in_place_residual_and_strided_views():
