@@ -659,7 +659,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& ta_mc, const CUtensorMap& t
   return launch_mc<BN, HD, 1>(ta, tw, twr, p, st);
 }
 
-int pick_bn(int N, const RmsArgs* rms) {
+int pick_bn(int N, int K, const RmsArgs* rms) {
   if (rms && rms->wq) {
     static const int heads3 = [] {                     // MDV2_GEMM_QKV216=0: two heads per tile (BN = 144)
       const char* e = getenv("MDV2_GEMM_QKV216");
@@ -680,6 +680,12 @@ int pick_bn(int N, const RmsArgs* rms) {
     const char* e = getenv("MDV2_GEMM_TAIL");
     return e ? atoi(e) : 1;
   }();
+  // long-K GEMMs whose N leaves a narrow last tile (fc2: N = 1152, K = 4608) take six equal 192-wide tiles: a tile
+  // lasts 36 us there, the pair that draws the half-width tile runs 18 us ahead of the four that share its A row block,
+  // and A left L2 in between — 8.0 GB read from DRAM for 3.9 algorithmic (ncu), against 1.4x with equal tiles; after the
+  // issue-chain fix the 192-wide tile is no slower there (1430 vs 1406 TF/s).  At K = 1152 the drift stays inside the L2
+  // window (1.59 of 1.55 GB) and 256-wide tiles + one narrow tile stay ahead
+  if (tail && N > 256 && N % 256 == 128 && N % 192 == 0 && K >= 2304) return 192;
   if (tail && N > 256 && N % 256 == 128) return 256;   // 256-wide tiles + one 128-wide last tile
   if (N % 192 == 0) return 192;
   if (N % 128 == 0) return 128;
@@ -692,7 +698,7 @@ bool mdv2_gemm_sm100_supported(int64_t M, int N, int K, int64_t lda, int64_t ldw
   if (M <= 0 || K % BK != 0 || K <= 0) return false;
   if (lda % 8 != 0 || ldw % 8 != 0 || ldo % 8 != 0 || N % 8 != 0) return false;
   if (rms && rms->wq && (rms->n_q % rms->head_dim != 0 || rms->n_k % rms->head_dim != 0)) return false;
-  return pick_bn(N, rms) != 0;
+  return pick_bn(N, K, rms) != 0;
 }
 
 int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void* out, int64_t ldo, int64_t M, int N,
@@ -702,7 +708,7 @@ int mdv2_gemm_sm100(const void* a, int64_t lda, const void* w, int64_t ldw, void
   MDV2_REQUIRE(((uintptr_t)a % 16 == 0) && ((uintptr_t)w % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
                    (!ep.res || ((uintptr_t)ep.res % 16 == 0 && ep.ldr % 8 == 0)),
                "gemm_sm100: operands must be 16-byte aligned");
-  const int bn = pick_bn(N, rms);
+  const int bn = pick_bn(N, K, rms);
   CUtensorMap ta, ta_mc, tw;
   int rc = mdv2_make_tmap_2d(&ta, a, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BM, BK);
   if (rc) return rc;
